@@ -256,6 +256,9 @@ static void jac_block(const Problem& P, const RBlock& b, int mode, bool skip_con
       for (int j = 0; j < pb.size; j++, col++) {
         long double x = store[pos[k] + j];
         long double h = 1e-7L * std::max(1.0L, std::fabs(x));
+        // RPC coefficients multiply monomials of pixel coordinates up to ~1e8: keep the
+        // denominator perturbation small (the Ceres-rule step is NOT small there).
+        if (b.kind == MVBA_BLOCK_CAM && k == 7 && pb.size > 5) h = 1e-13L;
         store[pos[k] + j] = x + h; eval_block<long double>(P, b, p, rp);
         store[pos[k] + j] = x - h; eval_block<long double>(P, b, p, rm);
         store[pos[k] + j] = x;
