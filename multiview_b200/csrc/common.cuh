@@ -1,0 +1,116 @@
+// common.cuh -- device-side view of one rig_calibrator optimisation pass and small FP64 helpers.
+// Part of libmvba.so (product).  Nothing here may include or link anything under oracle/.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/mvba.h"
+
+#define MVBA_MAX_SENSORS 16
+
+namespace mvba {
+
+// Per-camera table written by prep_cameras_kernel (one thread per camera image) and read by every
+// per-observation kernel.  All transcendental work of the pose interpolation
+// (reference rig_calibrator.cc:322-390, dense_map_utils.cc:315-329) happens once per camera here,
+// so the per-observation kernels are pure FMA + distortion.
+//   Xc = R X + t,   Z = R X
+//   dXc/dt0 = (1-alpha) Rrc      dXc/dq0_j = W0[:,j] x Z
+//   dXc/dt1 = alpha Rrc          dXc/dq1_j = W1[:,j] x Z
+//   dXc/dtrc = rig_on I          dXc/dqrc_j = Wrc[:,j] x (Xc - trc)
+//   dXc/doffset = dalpha (wa x Z + dt)
+struct CamTab {
+  double R[9], t[3];
+  double Rrc[9], trc[3];
+  double W0[12], W1[12], Wrc[12];  // 3x4 row-major, quaternion columns in storage order x y z w
+  double wa[3], dt[3];
+  double alpha, dalpha, rig_on, pad;
+};
+static_assert(sizeof(CamTab) == 70 * 8, "CamTab layout");
+
+// Per-sensor depth-to-image table (prep_sensors_kernel): Mc = s L m + td
+struct DepthTab {
+  double L[9], td[3], s;
+  double Wd[12];  // rigid: dMc/dq_j = s * Wd[:,j] x (L m)
+};
+
+struct SensorDev {
+  double half[2];
+  int nd;        // distortion block length (0 | 1 | 4 | 5 | 2n RPC)
+  int dist_off;  // offset of the block inside the distortion array
+  int rpc_deg;   // >0 for RPC
+  int nd_nz;     // number of distortion columns with a non-zero Jacobian (nd, or nd/2 for RPC)
+  // offsets of this sensor's parameter blocks inside the device parameter vector x
+  int x_rig, x_off, x_focal, x_center, x_dist, x_d2i, x_scale;
+  // first reduced-system column of each block, -1 when the block is constant
+  int c_rig, c_off, c_focal, c_center, c_dist, c_d2i, c_scale;
+};
+
+// Everything a kernel needs, passed by value (fits the 4 KB kernel parameter space).
+struct View {
+  int T, R, C, P, npose, no_rig, nd2i;
+  int64_t N;        // CAM blocks (observations)
+  int64_t n_dtri, n_dmesh, n_prior, n_pm;  // n_pm: MESH_TRI priors (stored first), rest are TRI
+  int nf, npose_cols, B;  // reduced system: nf = npose_cols + B
+  double robust_th, w_dtri, w_dmesh;
+  // parameter vector layout
+  int x_pose, x_ident, x_xyz, nx;
+  SensorDev sens[MVBA_MAX_SENSORS];
+  // cameras
+  const int32_t *cam_sensor, *cam_p0, *cam_p1;  // p0/p1: pose block index (p1 = -1: identity_vec)
+  const double *cam_bs, *cam_es, *cam_cs;
+  const int32_t* pose_col;  // npose: first reduced column or -1
+  // observations (track-major, reference order)
+  const int32_t *pid, *cid;
+  const float2* pix;
+  const int64_t* obs_row0;  // first residual row of the CAM block
+  // depth-tri / depth-mesh blocks: index of the originating observation
+  const int64_t *dtri_obs, *dmesh_obs, *dtri_row0, *dmesh_row0;
+  const float* depth_xyz;   // 3 per observation (only where used)
+  const double* mesh_xyz;   // 3 per observation
+  // priors
+  const int32_t* prior_pid; const double* prior_ref; const double *prior_w, *prior_th; const int64_t* prior_row0;
+  // per-track CSR over items
+  const int64_t* trk_obs0;      // P+1: first observation of each track
+  const int64_t* trk_dtri0;     // P+1
+  const int64_t* trk_dmesh0;    // P+1
+  const int64_t* trk_pm0;       // P+1: MESH_TRI priors of each track
+  const int64_t* trk_pt0;       // P+1: TRI priors of each track (indices into the merged list)
+};
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+__device__ __forceinline__ void cross3(const double* a, const double* b, double* o) {
+  o[0] = a[1] * b[2] - a[2] * b[1];
+  o[1] = a[2] * b[0] - a[0] * b[2];
+  o[2] = a[0] * b[1] - a[1] * b[0];
+}
+
+// 3x3 symmetric inverse from the 6 unique entries (xx xy xz yy yz zz); returns false when singular.
+__device__ __forceinline__ bool inv_sym3(const double* h, double* o) {
+  double c00 = h[3] * h[5] - h[4] * h[4];
+  double c01 = h[2] * h[4] - h[1] * h[5];
+  double c02 = h[1] * h[4] - h[2] * h[3];
+  double det = h[0] * c00 + h[1] * c01 + h[2] * c02;
+  double id = 1.0 / det;
+  o[0] = c00 * id; o[1] = c01 * id; o[2] = c02 * id;
+  o[3] = (h[0] * h[5] - h[2] * h[2]) * id;
+  o[4] = (h[1] * h[2] - h[0] * h[4]) * id;
+  o[5] = (h[0] * h[3] - h[1] * h[1]) * id;
+  return isfinite(id);
+}
+
+// Ceres CauchyLoss(a) + Corrector for rho'' <= 0 (reference rig_calibrator.cc:394-411 always picks
+// "cauchy"): cost 0.5 * b log(1 + s/b); residual and Jacobian rows scaled by sqrt(rho').
+__device__ __forceinline__ void cauchy(double a, double s, double* half_rho, double* sqrt_rho1) {
+  double b = a * a;
+  double sum = 1.0 + s / b;
+  *half_rho = 0.5 * b * log(sum);
+  *sqrt_rho1 = sqrt(1.0 / sum);
+}
+
+}  // namespace mvba

@@ -1,0 +1,277 @@
+// mvba.cu -- the C ABI of libmvba.so (include/mvba.h).  Single translation unit; all device code
+// is hand-written CUDA for sm_100a.  No CPU fallback and nothing from oracle/ is reachable here.
+#include <chrono>
+#include <cstdlib>
+
+#include "handle.cuh"
+#include "setup.cuh"
+#include "solver.cuh"
+
+namespace mvba {
+thread_local std::string g_last_error;
+
+static int ensure_device(int device) {
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n <= 0) { cudaGetLastError(); return fail(MVBA_ENODEVICE, "mvba: no CUDA device is visible (there is no CPU fallback)"); }
+  if (device < 0 || device >= n) return fail(MVBA_ENODEVICE, "mvba: CUDA device ordinal out of range");
+  cudaDeviceProp p;
+  if (cudaGetDeviceProperties(&p, device) != cudaSuccess) return fail(MVBA_ENODEVICE, "mvba: cannot query the CUDA device");
+  if (p.major < 10) return fail(MVBA_ENODEVICE, "mvba: libmvba.so carries sm_100a code only; device is sm_" + std::to_string(p.major) + std::to_string(p.minor));
+  return MVBA_OK;
+}
+
+static int ready(mvba_problem* h) {
+  if (!h) return fail(MVBA_EINVAL, "mvba: null handle");
+  int rc = ensure_device(h->device);
+  if (rc) return rc;
+  MVBA_CUDA(cudaSetDevice(h->device));
+  if (!h->stream) {
+    MVBA_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    cudaDeviceProp p; MVBA_CUDA(cudaGetDeviceProperties(&p, h->device));
+    h->sm_count = p.multiProcessorCount;
+  }
+  return setup(h);
+}
+
+static int check_device_error(mvba_problem* h) {
+  int err = 0;
+  MVBA_CUDA(cudaMemcpyAsync(&err, h->d_err.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+  MVBA_CUDA(cudaStreamSynchronize(h->stream));
+  if (err == MVBA_EBRACKET) return fail(MVBA_EBRACKET, "Out of bounds in interpolation. (rig_calibrator.cc:346)");
+  if (err) return fail(err, "mvba: device-side failure");
+  return MVBA_OK;
+}
+}  // namespace mvba
+
+using namespace mvba;
+
+extern "C" {
+
+const char* mvba_last_error(void) { return g_last_error.c_str(); }
+int mvba_abi_version(void) { return MVBA_ABI_VERSION; }
+int mvba_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  int ok = 0;
+  for (int i = 0; i < n; i++) { cudaDeviceProp p; if (cudaGetDeviceProperties(&p, i) == cudaSuccess && p.major >= 10) ok++; }
+  return ok;
+}
+
+int mvba_create(const mvba_config* cfg, int device, mvba_problem** out) {
+  if (!cfg || !out) return fail(MVBA_EINVAL, "mvba_create: null argument");
+  if (cfg->num_sensors <= 0 || cfg->num_sensors > MVBA_MAX_SENSORS || cfg->num_cameras < 0 || cfg->num_landmarks < 0 || cfg->num_ref_frames < 0)
+    return fail(MVBA_EINVAL, "mvba_create: bad sizes");
+  if (!(cfg->robust_threshold > 0)) return fail(MVBA_EINVAL, "mvba_create: robust_threshold must be positive");
+  mvba_problem* h = new mvba_problem();
+  h->cfg = *cfg; h->device = device;
+  h->sensors.assign(cfg->num_sensors, SensorHost());
+  *out = h;
+  return MVBA_OK;
+}
+
+int mvba_destroy(mvba_problem* h) {
+  if (!h) return MVBA_OK;
+  if (h->solver) { cudaSetDevice(h->device); solver_destroy(h); }
+  if (h->stream) { cudaSetDevice(h->device); cudaStreamDestroy(h->stream); }
+  delete h;
+  return MVBA_OK;
+}
+
+int mvba_set_sensor(mvba_problem* h, int32_t t, double w, double hgt, int32_t nd) {
+  if (!h || t < 0 || t >= h->cfg.num_sensors) return fail(MVBA_EINVAL, "mvba_set_sensor: bad sensor index");
+  if (nd < 0 || nd > MVBA_MAX_DISTORTION) return fail(MVBA_EINVAL, "mvba_set_sensor: bad distortion length");
+  h->sensors[t].w = w; h->sensors[t].h = hgt; h->sensors[t].nd = nd; h->built = false;
+  return MVBA_OK;
+}
+
+int mvba_set_params(mvba_problem* h, const mvba_params* p) {
+  if (!h || !p) return fail(MVBA_EINVAL, "mvba_set_params: null argument");
+  h->prm = *p; h->have_params = true; h->built = false;
+  return MVBA_OK;
+}
+
+int mvba_set_cameras(mvba_problem* h, int32_t n, const int32_t* sensor, const int32_t* beg, const int32_t* end, const double* stamp) {
+  if (!h || n != h->cfg.num_cameras || (n > 0 && (!sensor || !stamp))) return fail(MVBA_EINVAL, "mvba_set_cameras: bad argument");
+  if (!h->cfg.no_rig && n > 0 && (!beg || !end)) return fail(MVBA_EINVAL, "mvba_set_cameras: bracketing indices required with a rig");
+  h->cam_sensor.assign(sensor, sensor + n); h->cam_stamp.assign(stamp, stamp + n);
+  if (beg && end) { h->cam_beg.assign(beg, beg + n); h->cam_end.assign(end, end + n); } else { h->cam_beg.assign(n, 0); h->cam_end.assign(n, 0); }
+  h->have_cams = true; h->built = false;
+  return MVBA_OK;
+}
+
+int mvba_set_observations(mvba_problem* h, int64_t n, const int32_t* pid, const int32_t* cid, const float* pix,
+                          const uint8_t* has_depth, const float* depth_xyz, const uint8_t* has_mesh, const double* mesh_xyz) {
+  if (!h || n < 0 || (n > 0 && (!pid || !cid || !pix))) return fail(MVBA_EINVAL, "mvba_set_observations: bad argument");
+  h->nobs = n; h->opid.assign(pid, pid + n); h->ocid.assign(cid, cid + n); h->opix.assign(pix, pix + 2 * n);
+  h->ohasd.clear(); h->odepth.clear(); h->ohasm.clear(); h->omesh.clear();
+  if (has_depth && depth_xyz) { h->ohasd.assign(has_depth, has_depth + n); h->odepth.assign(depth_xyz, depth_xyz + 3 * n); }
+  if (has_mesh && mesh_xyz) { h->ohasm.assign(has_mesh, has_mesh + n); h->omesh.assign(mesh_xyz, mesh_xyz + 3 * n); }
+  h->have_obs = true; h->built = false;
+  return MVBA_OK;
+}
+
+int mvba_set_point_priors(mvba_problem* h, int32_t kind, int64_t n, const int32_t* pid, const double* ref, double w, double th) {
+  if (!h || (kind != MVBA_BLOCK_MESH_TRI && kind != MVBA_BLOCK_TRI) || n < 0 || (n > 0 && (!pid || !ref)))
+    return fail(MVBA_EINVAL, "mvba_set_point_priors: bad argument");
+  if (n > 0 && !(th > 0)) return fail(MVBA_EINVAL, "mvba_set_point_priors: robust threshold must be positive");
+  auto& pr = h->prior[kind == MVBA_BLOCK_MESH_TRI ? 0 : 1];
+  pr.pid.assign(pid, pid + n); pr.ref.assign(ref, ref + 3 * n); pr.w = w; pr.th = th; h->built = false;
+  return MVBA_OK;
+}
+
+int mvba_set_float_mask(mvba_problem* h, const mvba_float_mask* m) {
+  if (!h || !m) return fail(MVBA_EINVAL, "mvba_set_float_mask: null argument");
+  int T = h->cfg.num_sensors;
+  auto cp = [&](std::vector<uint8_t>& d, const uint8_t* s) { if (s) d.assign(s, s + T); else d.clear(); };
+  cp(h->m_focal, m->focal); cp(h->m_center, m->center); cp(h->m_dist, m->distortion); cp(h->m_rig, m->rig);
+  cp(h->m_d2i, m->depth_to_image); cp(h->m_poses, m->poses);
+  h->float_offsets = m->float_timestamp_offsets; h->float_scale = m->float_scale; h->have_mask = true; h->built = false;
+  return MVBA_OK;
+}
+
+int mvba_num_residuals(mvba_problem* h, int64_t* nres, int64_t* nblocks) {
+  int rc = ready(h); if (rc) return rc;
+  if (nres) *nres = h->nres;
+  if (nblocks) *nblocks = h->nblocks;
+  return MVBA_OK;
+}
+
+int mvba_residual_layout(mvba_problem* h, int32_t* kind, int64_t* row0, int64_t* src) {
+  int rc = ready(h); if (rc) return rc;
+  // merge the per-kind lists back into creation order by row0
+  struct Ent { int64_t row0; int32_t kind; int64_t src; };
+  std::vector<Ent> e; e.reserve(h->nblocks);
+  for (int64_t i = 0; i < h->nobs; i++) e.push_back({h->h_obs_row0[i], MVBA_BLOCK_CAM, i});
+  for (size_t j = 0; j < h->h_dtri_obs.size(); j++) e.push_back({h->h_dtri_row0[j], MVBA_BLOCK_DEPTH_TRI, h->h_dtri_obs[j]});
+  for (size_t j = 0; j < h->h_dmesh_obs.size(); j++) e.push_back({h->h_dmesh_row0[j], MVBA_BLOCK_DEPTH_MESH, h->h_dmesh_obs[j]});
+  int64_t n_pm = h->view.n_pm;
+  for (int64_t j = 0; j < h->view.n_prior; j++) e.push_back({h->h_prior_row0[j], j < n_pm ? MVBA_BLOCK_MESH_TRI : MVBA_BLOCK_TRI, j < n_pm ? j : j - n_pm});
+  std::sort(e.begin(), e.end(), [](const Ent& a, const Ent& b) { return a.row0 < b.row0; });
+  for (size_t i = 0; i < e.size(); i++) { if (kind) kind[i] = e[i].kind; if (row0) row0[i] = e[i].row0; if (src) src[i] = e[i].src; }
+  return MVBA_OK;
+}
+
+int mvba_upload(mvba_problem* h) {
+  int rc = ready(h); if (rc) return rc;
+  rc = upload_params(h); if (rc) return rc;
+  MVBA_CUDA(cudaStreamSynchronize(h->stream));
+  return MVBA_OK;
+}
+
+int mvba_evaluate(mvba_problem* h, int32_t apply_loss, double* cost, double* residuals) {
+  int rc = ready(h); if (rc) return rc;
+  rc = upload_params(h); if (rc) return rc;
+  const View& v = h->view;
+  MVBA_CUDA(cudaMemsetAsync(h->d_err.p, 0, sizeof(int), h->stream));
+  MVBA_CUDA(cudaMemsetAsync(h->d_scalars.p, 0, sizeof(double), h->stream));
+  run_prep(h, h->d_x.p);
+  double* dres = nullptr;
+  if (residuals) { MVBA_CUDA(h->d_resid.alloc((size_t)h->nres)); dres = h->d_resid.p; }
+  int64_t total = v.N + v.n_dtri + v.n_dmesh + v.n_prior;
+  int grid = (int)std::min<int64_t>((total + 255) / 256, (int64_t)h->sm_count * 8);
+  if (grid < 1) grid = 1;
+  residual_kernel<<<grid, 256, 0, h->stream>>>(v, h->d_x.p, h->d_tab.p, h->d_dtab.p, apply_loss, h->d_scalars.p, dres);
+  h->launches++;
+  MVBA_CUDA(cudaGetLastError());
+  double c = 0;
+  MVBA_CUDA(cudaMemcpyAsync(&c, h->d_scalars.p, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  if (residuals && h->nres > 0) MVBA_CUDA(cudaMemcpyAsync(residuals, dres, sizeof(double) * h->nres, cudaMemcpyDeviceToHost, h->stream));
+  rc = check_device_error(h); if (rc) return rc;
+  if (cost) *cost = c;
+  return MVBA_OK;
+}
+
+static int kind_width(mvba_problem* h, int kind) {
+  int ndmax = 0;
+  for (auto& s : h->sensors) ndmax = std::max(ndmax, s.nd);
+  switch (kind) {
+    case MVBA_BLOCK_CAM: return 28 + ndmax;
+    case MVBA_BLOCK_DEPTH_TRI: return 21 + h->nd2i() + 1 + 3 + 1;
+    case MVBA_BLOCK_DEPTH_MESH: return 21 + h->nd2i() + 1 + 1;
+    default: return 3;
+  }
+}
+
+int mvba_jacobian_width(mvba_problem* h, int32_t kind, int32_t* w) {
+  if (!h || !w || kind < 0 || kind > MVBA_BLOCK_TRI) return fail(MVBA_EINVAL, "mvba_jacobian_width: bad argument");
+  *w = kind_width(h, kind);
+  return MVBA_OK;
+}
+
+int mvba_evaluate_jacobian(mvba_problem* h, int32_t kind, int64_t first, int64_t count, double* residuals, double* jac) {
+  int rc = ready(h); if (rc) return rc;
+  if (kind < 0 || kind > MVBA_BLOCK_TRI || !jac) return fail(MVBA_EINVAL, "mvba_evaluate_jacobian: bad argument");
+  const View& v = h->view;
+  int64_t avail = kind == MVBA_BLOCK_CAM ? v.N : kind == MVBA_BLOCK_DEPTH_TRI ? v.n_dtri : kind == MVBA_BLOCK_DEPTH_MESH ? v.n_dmesh
+                  : kind == MVBA_BLOCK_MESH_TRI ? v.n_pm : v.n_prior - v.n_pm;
+  if (first < 0 || count < 0 || first + count > avail) return fail(MVBA_EINVAL, "mvba_evaluate_jacobian: range out of bounds");
+  if (count == 0) return MVBA_OK;
+  rc = upload_params(h); if (rc) return rc;
+  MVBA_CUDA(cudaMemsetAsync(h->d_err.p, 0, sizeof(int), h->stream));
+  run_prep(h, h->d_x.p);
+  const int W = kind_width(h, kind), rows = kind == MVBA_BLOCK_CAM ? 2 : 3;
+  DBuf<double> dJ, dr;
+  MVBA_CUDA(dJ.alloc((size_t)count * rows * W)); MVBA_CUDA(dr.alloc((size_t)count * rows));
+  MVBA_CUDA(dJ.zero(h->stream));
+  jacobian_store_kernel<<<(unsigned)((count + 127) / 128), 128, 0, h->stream>>>(v, h->d_x.p, h->d_tab.p, h->d_dtab.p, kind, first, count, W, dr.p, dJ.p);
+  h->launches++;
+  MVBA_CUDA(cudaGetLastError());
+  MVBA_CUDA(cudaMemcpyAsync(jac, dJ.p, sizeof(double) * count * rows * W, cudaMemcpyDeviceToHost, h->stream));
+  if (residuals) MVBA_CUDA(cudaMemcpyAsync(residuals, dr.p, sizeof(double) * count * rows, cudaMemcpyDeviceToHost, h->stream));
+  return check_device_error(h);
+}
+
+int mvba_bench_jacobian(mvba_problem* h, int32_t repeats, float* ms_total) {
+  int rc = ready(h); if (rc) return rc;
+  const View& v = h->view;
+  if (v.N == 0 || repeats <= 0) return fail(MVBA_EINVAL, "mvba_bench_jacobian: nothing to do");
+  const int W = kind_width(h, MVBA_BLOCK_CAM);
+  DBuf<double> dJ, dr;
+  MVBA_CUDA(dJ.alloc((size_t)v.N * 2 * W)); MVBA_CUDA(dr.alloc((size_t)v.N * 2));
+  run_prep(h, h->d_x.p);
+  cudaEvent_t e0, e1;
+  MVBA_CUDA(cudaEventCreate(&e0)); MVBA_CUDA(cudaEventCreate(&e1));
+  MVBA_CUDA(cudaEventRecord(e0, h->stream));
+  for (int i = 0; i < repeats; i++) {
+    jacobian_store_kernel<<<(unsigned)((v.N + 127) / 128), 128, 0, h->stream>>>(v, h->d_x.p, h->d_tab.p, h->d_dtab.p, MVBA_BLOCK_CAM, 0, v.N, W, dr.p, dJ.p);
+    h->launches++;
+  }
+  MVBA_CUDA(cudaEventRecord(e1, h->stream));
+  MVBA_CUDA(cudaEventSynchronize(e1));
+  MVBA_CUDA(cudaEventElapsedTime(ms_total, e0, e1));
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  MVBA_CUDA(cudaGetLastError());
+  return MVBA_OK;
+}
+
+int mvba_solve_options_init(mvba_solve_options* o) {
+  if (!o) return fail(MVBA_EINVAL, "mvba_solve_options_init: null argument");
+  // rig_calibrator.cc:1910-1918 + Ceres 1.14 Solver::Options defaults
+  o->max_num_iterations = 20; o->parameter_tolerance = 1e-12; o->function_tolerance = 1e-16; o->gradient_tolerance = 1e-16;
+  o->initial_trust_region_radius = 1e4; o->max_trust_region_radius = 1e16; o->min_trust_region_radius = 1e-32;
+  o->min_relative_decrease = 1e-3; o->min_lm_diagonal = 1e-6; o->max_lm_diagonal = 1e32; o->eta = 0.1;
+  o->max_linear_solver_iterations = 500; o->min_linear_solver_iterations = 0; o->jacobi_scaling = 1;
+  o->linear_solver = 0; o->preconditioner = 0; o->verbose = 0;
+  return MVBA_OK;
+}
+
+int mvba_solve(mvba_problem* h, const mvba_solve_options* o, mvba_summary* s, mvba_iteration* its, int32_t max_its) {
+  int rc = ready(h); if (rc) return rc;
+  if (!o || !s) return fail(MVBA_EINVAL, "mvba_solve: null argument");
+  return solver_solve(h, *o, s, its, max_its);
+}
+
+int mvba_bench_build(mvba_problem* h, int32_t repeats, float* ms_total) {
+  int rc = ready(h); if (rc) return rc;
+  return solver_bench_build(h, repeats, ms_total);
+}
+
+int mvba_nccl_unique_id(uint8_t id128[128]) { return comm_unique_id(id128); }
+int mvba_comm_init(mvba_problem* h, int32_t rank, int32_t nranks, const uint8_t id128[128]) {
+  if (!h) return fail(MVBA_EINVAL, "mvba_comm_init: null handle");
+  int rc = ready(h); if (rc) return rc;
+  return comm_init(h, rank, nranks, id128);
+}
+
+}  // extern "C"
