@@ -1,0 +1,259 @@
+// kernels_pcg.cuh -- LM damping of the reduced system, block-Jacobi preconditioner and the
+// preconditioned conjugate-gradient iteration (Ceres 1.14 ConjugateGradientsSolver semantics:
+// Q-based stopping with eta, residual refresh every 10 iterations), all on device.
+#pragma once
+#include "kernels_build.cuh"
+#include "kernels_eval.cuh"
+
+namespace mvba {
+
+// Block-sparse symmetric structure for S x: each block row lists (col block, slot, transposed).
+struct Bsr {
+  const int32_t *row_ptr, *col, *slot;  // slot >= 0: Spp[slot] as stored; slot < 0: transpose of Spp[-slot-1]
+  int nb;
+};
+
+// Scalars of one PCG solve; slots indexed by iteration to avoid re-zeroing races.
+//  per iteration it: [0] rho = r.z   [1] pq = p.q   [2] Q1 = -x.(b+r)
+struct PcgScal { double* it; int* done; int* iters; double* bnorm2; };
+
+// --- finalize: damping, mirroring, preconditioner ------------------------------------------
+// One thread per reduced column: D^2 = clamp(diag F'F)/radius added to the diagonal of S.
+__global__ void damp_kernel(Reduced S, double radius, double min_diag, double max_diag, double* __restrict__ Dsq) {
+  int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= S.nf) return;
+  double d = fmin(fmax(S.diagF[g], min_diag), max_diag) / radius;
+  Dsq[g] = d;
+  if (g < S.npc) {
+    int u = g / 7, r = g - 7 * u;
+    int slot = S.pairtab[(size_t)u * S.nb + u];
+    S.Spp[(size_t)slot * 49 + r * 8] += d;
+    if (S.Fpp) S.Fpp[(size_t)u * 49 + r * 8] += d;
+  } else {
+    int b = g - S.npc;
+    S.Sbb[(size_t)b * S.B + b] += d;
+    if (S.Fbb) S.Fbb[(size_t)b * S.B + b] += d;
+  }
+}
+
+// In-register inverse of a symmetric positive definite 7x7 given its upper triangle (row-major 49).
+__device__ inline void inv7_upper(const double* __restrict__ src, double* __restrict__ dst) {
+  double A[49];
+#pragma unroll
+  for (int i = 0; i < 7; i++)
+#pragma unroll
+    for (int j = 0; j < 7; j++) A[7 * i + j] = (j >= i) ? src[7 * i + j] : src[7 * j + i];
+  // Gauss-Jordan without pivoting (SPD)
+#pragma unroll
+  for (int k = 0; k < 7; k++) {
+    double piv = 1.0 / A[8 * k];
+#pragma unroll
+    for (int j = 0; j < 7; j++) A[7 * k + j] = (j == k) ? piv : A[7 * k + j] * piv;
+#pragma unroll
+    for (int i = 0; i < 7; i++) {
+      if (i == k) continue;
+      double f = A[7 * i + k];
+#pragma unroll
+      for (int j = 0; j < 7; j++) A[7 * i + j] = (j == k) ? -f * piv : A[7 * i + j] - f * A[7 * k + j];
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 49; i++) dst[i] = A[i];
+}
+
+// One thread per pose block: mirror the diagonal block of S and invert the preconditioner block.
+__global__ void precond_pose_kernel(Reduced S, int use_F, double* __restrict__ Minv) {
+  int u = blockIdx.x * blockDim.x + threadIdx.x;
+  if (u >= S.nb) return;
+  int slot = S.pairtab[(size_t)u * S.nb + u];
+  double* D = S.Spp + (size_t)slot * 49;
+  for (int i = 0; i < 7; i++) for (int j = 0; j < i; j++) D[7 * i + j] = D[7 * j + i];
+  inv7_upper(use_F ? S.Fpp + (size_t)u * 49 : D, Minv + (size_t)u * 49);
+}
+
+// One CTA: mirror Sbb, then invert the border block (B x B, SPD) by Gauss-Jordan in global memory.
+__global__ void __launch_bounds__(256) precond_border_kernel(Reduced S, int use_F, double* __restrict__ Minv, double* __restrict__ work) {
+  const int B = S.B, tid = threadIdx.x, nt = blockDim.x;
+  for (int i = tid; i < B * B; i += nt) { int r = i / B, c = i - r * B; if (c < r) S.Sbb[i] = S.Sbb[(size_t)c * B + r]; }
+  __syncthreads();
+  const double* src = use_F ? S.Fbb : S.Sbb;
+  for (int i = tid; i < B * B; i += nt) { int r = i / B, c = i - r * B; work[i] = (c >= r) ? src[i] : src[(size_t)c * B + r]; Minv[i] = (r == c) ? 1.0 : 0.0; }
+  __syncthreads();
+  __shared__ double piv_s;
+  for (int k = 0; k < B; k++) {
+    if (tid == 0) piv_s = 1.0 / work[(size_t)k * B + k];
+    __syncthreads();
+    double piv = piv_s;
+    for (int j = tid; j < B; j += nt) { work[(size_t)k * B + j] *= piv; Minv[(size_t)k * B + j] *= piv; }
+    __syncthreads();
+    for (int i = tid; i < B * B; i += nt) {
+      int r = i / B, c = i - r * B;
+      if (r == k) continue;
+      double f = work[(size_t)r * B + k];
+      if (f != 0.0) {
+        Minv[i] -= f * Minv[(size_t)k * B + c];
+        if (c != k) work[i] -= f * work[(size_t)k * B + c];
+      }
+    }
+    __syncthreads();
+    for (int r = tid; r < B; r += nt) if (r != k) work[(size_t)r * B + k] = 0.0;
+    __syncthreads();
+  }
+}
+
+// --- S x ----------------------------------------------------------------------------------
+// One warp per pose block row (lanes over the row's blocks), then warps for the border rows.
+// y must have its border part zeroed before the launch (pose rows add S_pb' x_pose atomically).
+__global__ void __launch_bounds__(256) spmv_kernel(Reduced S, Bsr A, const double* __restrict__ x, double* __restrict__ y,
+                                                    const int* __restrict__ done) {
+  if (done && *done) return;
+  const int lane = threadIdx.x & 31;
+  const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int B = S.B;
+  if (w < A.nb) {
+    double acc[7] = {0, 0, 0, 0, 0, 0, 0};
+    for (int e = A.row_ptr[w] + lane; e < A.row_ptr[w + 1]; e += 32) {
+      int c = A.col[e], sl = A.slot[e];
+      const double* xb = x + 7 * c;
+      double xv[7];
+#pragma unroll
+      for (int k = 0; k < 7; k++) xv[k] = xb[k];
+      if (sl >= 0) {
+        const double* M = S.Spp + (size_t)sl * 49;
+#pragma unroll
+        for (int r = 0; r < 7; r++)
+#pragma unroll
+          for (int k = 0; k < 7; k++) acc[r] += M[7 * r + k] * xv[k];
+      } else {
+        const double* M = S.Spp + (size_t)(-sl - 1) * 49;
+#pragma unroll
+        for (int k = 0; k < 7; k++)
+#pragma unroll
+          for (int r = 0; r < 7; r++) acc[r] += M[7 * k + r] * xv[k];
+      }
+    }
+    // border columns of this block row, and their transpose contribution to the border rows
+    double xr[7];
+#pragma unroll
+    for (int r = 0; r < 7; r++) xr[r] = x[7 * w + r];
+    for (int b = lane; b < B; b += 32) {
+      double xb = x[S.npc + b], t = 0;
+#pragma unroll
+      for (int r = 0; r < 7; r++) { double s = S.Spb[(size_t)(7 * w + r) * B + b]; acc[r] += s * xb; t += s * xr[r]; }
+      atomicAdd(y + S.npc + b, t);
+    }
+#pragma unroll
+    for (int r = 0; r < 7; r++) acc[r] = warp_sum(acc[r]);
+    if (lane == 0) {
+#pragma unroll
+      for (int r = 0; r < 7; r++) y[7 * w + r] = acc[r];
+    }
+  } else {
+    int b = w - A.nb;  // border row
+    if (b >= B) return;
+    double t = 0;
+    for (int c = lane; c < B; c += 32) t += S.Sbb[(size_t)b * B + c] * x[S.npc + c];
+    t = warp_sum(t);
+    if (lane == 0) atomicAdd(y + S.npc + b, t);
+  }
+}
+
+// --- PCG steps ------------------------------------------------------------------------------
+// init: x = 0, r = b, |b|^2 ; border of q zeroed for the first SpMV
+__global__ void pcg_init_kernel(int nf, int npc, const double* __restrict__ b, double* __restrict__ x, double* __restrict__ r,
+                                double* __restrict__ q, PcgScal sc) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  double v = 0;
+  if (i < nf) { x[i] = 0; r[i] = b[i]; v = b[i] * b[i]; if (i >= npc) q[i] = 0; }
+  block_accumulate(v, sc.bnorm2);
+}
+
+// z = M^-1 r (block Jacobi), rho_it = r.z.  One thread per reduced column.
+__global__ void __launch_bounds__(256) pcg_precond_kernel(Reduced S, const double* __restrict__ Mpp, const double* __restrict__ Mbb,
+                                                           const double* __restrict__ r, double* __restrict__ z, PcgScal sc, int it) {
+  if (*sc.done) return;
+  int g = blockIdx.x * blockDim.x + threadIdx.x;
+  double v = 0;
+  if (g < S.nf) {
+    double s = 0;
+    if (g < S.npc) {
+      int u = g / 7, k = g - 7 * u;
+      const double* M = Mpp + (size_t)u * 49 + 7 * k;
+      const double* rb = r + 7 * u;
+#pragma unroll
+      for (int j = 0; j < 7; j++) s += M[j] * rb[j];
+    } else {
+      int b = g - S.npc;
+      for (int j = 0; j < S.B; j++) s += Mbb[(size_t)b * S.B + j] * r[S.npc + j];
+    }
+    z[g] = s;
+    v = s * r[g];
+  }
+  block_accumulate(v, sc.it + 4 * it);
+}
+
+// p = z + beta p   (beta = rho_it / rho_{it-1}); zero the border part of q for the SpMV.
+__global__ void pcg_dir_kernel(int nf, int npc, const double* __restrict__ z, double* __restrict__ p, double* __restrict__ q,
+                               PcgScal sc, int it) {
+  if (*sc.done) return;
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nf) return;
+  double rho = sc.it[4 * it];
+  if (i == 0 && (rho == 0.0 || !isfinite(rho))) { *sc.done = 2; }
+  double beta = (it == 1) ? 0.0 : rho / sc.it[4 * (it - 1)];
+  p[i] = z[i] + beta * p[i];
+  if (i >= npc) q[i] = 0;
+}
+
+// pq_it = p.q
+__global__ void pcg_dot_kernel(int nf, const double* __restrict__ p, const double* __restrict__ q, PcgScal sc, int it) {
+  if (*sc.done) return;
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  double v = (i < nf) ? p[i] * q[i] : 0.0;
+  block_accumulate(v, sc.it + 4 * it + 1);
+}
+
+// x += alpha p ; r -= alpha q ; Q1_it = -x.(b + r)
+__global__ void pcg_update_kernel(int nf, const double* __restrict__ b, const double* __restrict__ p, const double* __restrict__ q,
+                                  double* __restrict__ x, double* __restrict__ r, PcgScal sc, int it) {
+  if (*sc.done) return;
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  double pq = sc.it[4 * it + 1], rho = sc.it[4 * it];
+  double v = 0;
+  if (pq <= 0.0 || !isfinite(pq)) {  // "matrix is indefinite": stop, keep the last iterate
+    if (i == 0) *sc.done = 3;
+    return;
+  }
+  double alpha = rho / pq;
+  if (i < nf) {
+    double xi = x[i] + alpha * p[i];
+    double ri = r[i] - alpha * q[i];
+    x[i] = xi; r[i] = ri;
+    v = -xi * (b[i] + ri);
+  }
+  block_accumulate(v, sc.it + 4 * it + 2);
+}
+
+// r = b - q (q = S x), Q1 recomputed (residual_reset_period = 10)
+__global__ void pcg_refresh_kernel(int nf, const double* __restrict__ b, const double* __restrict__ q, const double* __restrict__ x,
+                                   double* __restrict__ r, PcgScal sc, int it) {
+  if (*sc.done) return;
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  double v = 0;
+  if (i < nf) { double ri = b[i] - q[i]; r[i] = ri; v = -x[i] * (b[i] + ri); }
+  block_accumulate(v, sc.it + 4 * it + 3);
+}
+
+// Single thread: Ceres' Q-test  zeta = it (Q1 - Q0) / Q1 < eta.
+__global__ void pcg_check_kernel(PcgScal sc, int it, int refreshed, double eta, int min_it, int max_it) {
+  if (*sc.done) return;
+  double Q1 = refreshed ? sc.it[4 * it + 3] : sc.it[4 * it + 2];
+  if (refreshed) sc.it[4 * it + 2] = Q1;
+  double Q0 = (it == 1) ? 0.0 : sc.it[4 * (it - 1) + 2];
+  double zeta = it * (Q1 - Q0) / Q1;
+  *sc.iters = it;
+  if (zeta < eta && it >= min_it) *sc.done = 1;
+  else if (it >= max_it) *sc.done = 4;
+}
+
+}  // namespace mvba

@@ -34,14 +34,6 @@ static int ready(mvba_problem* h) {
   return setup(h);
 }
 
-static int check_device_error(mvba_problem* h) {
-  int err = 0;
-  MVBA_CUDA(cudaMemcpyAsync(&err, h->d_err.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
-  MVBA_CUDA(cudaStreamSynchronize(h->stream));
-  if (err == MVBA_EBRACKET) return fail(MVBA_EBRACKET, "Out of bounds in interpolation. (rig_calibrator.cc:346)");
-  if (err) return fail(err, "mvba: device-side failure");
-  return MVBA_OK;
-}
 }  // namespace mvba
 
 using namespace mvba;

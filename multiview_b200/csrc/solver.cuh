@@ -1,11 +1,199 @@
-// solver.cuh -- placeholder, replaced by the LM solver.
+// solver.cuh -- host orchestration of the device Levenberg-Marquardt loop:
+//   fused build (Jacobian + J'J + Schur) -> [NCCL allreduce] -> damping + block-Jacobi -> PCG
+//   -> landmark back-substitution -> candidate cost -> accept/reject + radius on device.
+// Follows Ceres 1.14 TrustRegionMinimizer with ITERATIVE_SCHUR as configured by the reference
+// (rig_calibrator.cc:1910-1918); the Schur complement is formed explicitly instead of implicitly.
 #pragma once
+#include <dlfcn.h>
+
+#include <chrono>
+
 #include "handle.cuh"
+#include "kernels_lm.cuh"
+
 namespace mvba {
-struct Solver {};
-inline void solver_destroy(mvba_problem* h) { delete h->solver; h->solver = nullptr; }
-inline int solver_solve(mvba_problem*, const mvba_solve_options&, mvba_summary*, mvba_iteration*, int) { return fail(MVBA_ESTATE, "solver not built"); }
-inline int solver_bench_build(mvba_problem*, int, float*) { return fail(MVBA_ESTATE, "solver not built"); }
-inline int comm_unique_id(uint8_t*) { return fail(MVBA_ENCCL, "nccl not built"); }
-inline int comm_init(mvba_problem*, int, int, const uint8_t*) { return fail(MVBA_ENCCL, "nccl not built"); }
+
+// ---- NCCL, loaded at run time so that libmvba.so has no link-time dependency on it ----
+struct Nccl {
+  void* lib = nullptr;
+  int (*GetUniqueId)(void*) = nullptr;
+  int (*CommInitRank)(void**, int, uint8_t[128], int) = nullptr;  // ncclUniqueId is passed by value (128 bytes)
+  int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+  int (*CommDestroy)(void*) = nullptr;
+  const char* (*GetErrorString)(int) = nullptr;
+};
+struct NcclId { char b[128]; };
+inline Nccl& nccl() {
+  static Nccl n;
+  if (!n.lib) {
+    n.lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!n.lib) n.lib = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (n.lib) {
+      n.GetUniqueId = (int (*)(void*))dlsym(n.lib, "ncclGetUniqueId");
+      n.CommInitRank = (int (*)(void**, int, uint8_t[128], int))dlsym(n.lib, "ncclCommInitRank");
+      n.AllReduce = (int (*)(const void*, void*, size_t, int, int, void*, cudaStream_t))dlsym(n.lib, "ncclAllReduce");
+      n.CommDestroy = (int (*)(void*))dlsym(n.lib, "ncclCommDestroy");
+      n.GetErrorString = (const char* (*)(int))dlsym(n.lib, "ncclGetErrorString");
+    }
+  }
+  return n;
 }
+inline int comm_unique_id(uint8_t* id128) {
+  Nccl& n = nccl();
+  if (!n.lib || !n.GetUniqueId) return fail(MVBA_ENCCL, "mvba: libnccl.so.2 not loadable");
+  int rc = n.GetUniqueId(id128);
+  return rc ? fail(MVBA_ENCCL, std::string("ncclGetUniqueId: ") + n.GetErrorString(rc)) : MVBA_OK;
+}
+inline int comm_init(mvba_problem* h, int rank, int nranks, const uint8_t* id128) {
+  if (nranks <= 1) { h->rank = 0; h->nranks = 1; return MVBA_OK; }
+  Nccl& n = nccl();
+  if (!n.lib || !n.CommInitRank) return fail(MVBA_ENCCL, "mvba: libnccl.so.2 not loadable");
+  typedef int (*init_t)(void**, int, NcclId, int);
+  NcclId id; std::memcpy(id.b, id128, 128);
+  int rc = ((init_t)dlsym(n.lib, "ncclCommInitRank"))(&h->nccl_comm, nranks, id, rank);
+  if (rc) return fail(MVBA_ENCCL, std::string("ncclCommInitRank: ") + n.GetErrorString(rc));
+  h->rank = rank; h->nranks = nranks;
+  return MVBA_OK;
+}
+// op: 0 sum, 2 max (ncclRedOp_t); dtype 8 = ncclFloat64, 5 = ncclUint64
+inline int allreduce(mvba_problem* h, void* buf, size_t n, int dtype, int op) {
+  if (h->nranks <= 1 || n == 0) return MVBA_OK;
+  Nccl& nc = nccl();
+  int rc = nc.AllReduce(buf, buf, n, dtype, op, h->nccl_comm, h->stream);
+  return rc ? fail(MVBA_ENCCL, std::string("ncclAllReduce: ") + nc.GetErrorString(rc)) : MVBA_OK;
+}
+
+struct Solver {
+  int nb = 0, npc = 0, B = 0, nf = 0;
+  int64_t nslots = 0, nnzb = 0;
+  int maxposes = 1, maxitems = 1, maxdz = 1, vwmax = MVBA_VPOSE + 4;
+  DBuf<int32_t> pairtab, row_ptr, col, slot, xcol;
+  DBuf<double> red;  // [Spp | Spb | Sbb | Fpp | Fbb | g | diagF | rhs | cost]  (one allreduce)
+  size_t o_Spp = 0, o_Spb = 0, o_Sbb = 0, o_Fpp = 0, o_Fbb = 0, o_g = 0, o_diagF = 0, o_rhs = 0, o_cost = 0, red_n = 0;
+  DBuf<double> Dsq, Mpp, Mbb, work, jscale_f, jscale_e, Hinv, ge, diagE, lo, hi;
+  DBuf<double> y, r, z, p, q, ye, lm, pcg_scal;
+  DBuf<int> pcg_flags;
+  mvba_iteration* rec = nullptr;  // pinned
+  int* flags_host = nullptr;      // pinned
+  size_t smem_build = 0, smem_backsub = 0;
+  int wpb_build = 8, wpb_backsub = 8, grid_build = 1, grid_backsub = 1;
+  bool with_F = false;
+  Reduced R{};
+  Bsr A{};
+};
+
+inline void solver_destroy(mvba_problem* h) {
+  if (!h->solver) return;
+  if (h->solver->rec) cudaFreeHost(h->solver->rec);
+  if (h->solver->flags_host) cudaFreeHost(h->solver->flags_host);
+  delete h->solver; h->solver = nullptr;
+}
+
+// Structure analysis: which pose-block pairs are co-observed by some track, shared-memory sizing.
+inline int solver_prepare(mvba_problem* h, bool with_F) {
+  if (h->solver && h->solver->with_F == with_F) return MVBA_OK;
+  solver_destroy(h);
+  Solver* s = new Solver();
+  h->solver = s;
+  const View& v = h->view;
+  s->with_F = with_F;
+  s->npc = v.npose_cols; s->nb = v.npose_cols / 7; s->B = v.B; s->nf = v.nf;
+  const int nb = s->nb;
+  if ((size_t)nb * nb > ((size_t)1 << 31)) return fail(MVBA_EINVAL, "mvba: too many free pose blocks for the dense pair table");
+  std::vector<uint8_t> flag((size_t)nb * nb, 0);
+  std::vector<int> uniq;
+  int maxposes = 1, maxitems = 1;
+  for (int p = 0; p < v.P; p++) {
+    uniq.clear();
+    for (int64_t i = h->h_trk_obs0[p]; i < h->h_trk_obs0[p + 1]; i++) {
+      int c = h->ocid[i];
+      for (int w = 0; w < 2; w++) {
+        int pose = w == 0 ? h->h_cam_p0[c] : h->h_cam_p1[c];
+        if (pose < 0) continue;
+        int pc = h->h_pose_col[pose];
+        if (pc < 0) continue;
+        int u = pc / 7;
+        if (std::find(uniq.begin(), uniq.end(), u) == uniq.end()) uniq.push_back(u);
+      }
+    }
+    for (size_t a = 0; a < uniq.size(); a++) for (size_t b = 0; b < uniq.size(); b++) { int u1 = uniq[a], u2 = uniq[b]; if (u1 <= u2) flag[(size_t)u1 * nb + u2] = 1; }
+    maxposes = std::max(maxposes, (int)uniq.size());
+    int items = (int)(h->h_trk_obs0[p + 1] - h->h_trk_obs0[p] + h->h_trk_dtri0[p + 1] - h->h_trk_dtri0[p] + h->h_trk_dmesh0[p + 1] - h->h_trk_dmesh0[p] +
+                      h->h_trk_pm0[p + 1] - h->h_trk_pm0[p] + h->h_trk_pt0[p + 1] - h->h_trk_pt0[p]);
+    maxitems = std::max(maxitems, items);
+  }
+  for (int u = 0; u < nb; u++) flag[(size_t)u * nb + u] = 1;  // diagonal always present (damping)
+  std::vector<int32_t> pairtab((size_t)nb * nb, -1), row_ptr(nb + 1, 0), col, slot;
+  int64_t ns = 0;
+  std::vector<std::vector<std::pair<int, int>>> rows(nb);
+  for (int u1 = 0; u1 < nb; u1++)
+    for (int u2 = u1; u2 < nb; u2++)
+      if (flag[(size_t)u1 * nb + u2]) {
+        pairtab[(size_t)u1 * nb + u2] = (int32_t)ns;
+        rows[u1].push_back({u2, (int)ns});
+        if (u1 != u2) rows[u2].push_back({u1, -(int)ns - 1});
+        ns++;
+      }
+  for (int u = 0; u < nb; u++) {
+    std::sort(rows[u].begin(), rows[u].end());
+    row_ptr[u + 1] = row_ptr[u] + (int)rows[u].size();
+    for (auto& e : rows[u]) { col.push_back(e.first); slot.push_back(e.second); }
+  }
+  s->nslots = ns; s->nnzb = (int64_t)col.size();
+  s->maxposes = maxposes; s->maxitems = maxitems;
+  int maxdz = 1, vw = MVBA_VPOSE + 3;
+  for (int t = 0; t < v.T; t++) { maxdz = std::max(maxdz, v.sens[t].nd_nz); vw = std::max(vw, MVBA_VPOSE + 3 + v.sens[t].nd_nz); }
+  vw = std::max(vw, MVBA_VPOSE + v.nd2i + 1);
+  s->maxdz = maxdz; s->vwmax = vw;
+  MVBA_CUDA(s->pairtab.upload(pairtab)); MVBA_CUDA(s->row_ptr.upload(row_ptr)); MVBA_CUDA(s->col.upload(col)); MVBA_CUDA(s->slot.upload(slot));
+  MVBA_CUDA(s->xcol.upload(h->h_xcol));
+  if (h->bounded) { MVBA_CUDA(s->lo.upload(h->h_lo)); MVBA_CUDA(s->hi.upload(h->h_hi)); }
+  // one contiguous buffer for everything that is summed across ranks
+  size_t o = 0;
+  auto take = [&](size_t n) { size_t r = o; o += (n + 1) & ~(size_t)1; return r; };
+  s->o_Spp = take((size_t)ns * 49); s->o_Spb = take((size_t)s->npc * s->B); s->o_Sbb = take((size_t)s->B * s->B);
+  s->o_Fpp = take(with_F ? (size_t)nb * 49 : 0); s->o_Fbb = take(with_F ? (size_t)s->B * s->B : 0);
+  s->o_g = take(s->nf); s->o_diagF = take(s->nf); s->o_rhs = take(s->nf); s->o_cost = take(2);
+  s->red_n = o;
+  MVBA_CUDA(s->red.alloc(o));
+  const int nf = std::max(s->nf, 1);
+  MVBA_CUDA(s->Dsq.alloc(nf)); MVBA_CUDA(s->Mpp.alloc((size_t)std::max(nb, 1) * 49)); MVBA_CUDA(s->Mbb.alloc((size_t)std::max(s->B * s->B, 1)));
+  MVBA_CUDA(s->work.alloc((size_t)std::max(s->B * s->B, 1)));
+  MVBA_CUDA(s->jscale_f.alloc(nf)); MVBA_CUDA(s->jscale_e.alloc((size_t)3 * std::max(v.P, 1)));
+  MVBA_CUDA(s->Hinv.alloc((size_t)6 * std::max(v.P, 1))); MVBA_CUDA(s->ge.alloc((size_t)3 * std::max(v.P, 1)));
+  MVBA_CUDA(s->diagE.alloc((size_t)3 * std::max(v.P, 1))); MVBA_CUDA(s->ye.alloc((size_t)3 * std::max(v.P, 1)));
+  MVBA_CUDA(s->y.alloc(nf)); MVBA_CUDA(s->r.alloc(nf)); MVBA_CUDA(s->z.alloc(nf)); MVBA_CUDA(s->p.alloc(nf)); MVBA_CUDA(s->q.alloc(nf));
+  MVBA_CUDA(s->lm.alloc(LM_NSLOTS)); MVBA_CUDA(s->pcg_flags.alloc(4));
+  MVBA_CUDA(cudaMallocHost((void**)&s->rec, sizeof(mvba_iteration)));
+  MVBA_CUDA(cudaMallocHost((void**)&s->flags_host, 4 * sizeof(int)));
+  Reduced& R = s->R;
+  double* rb = s->red.p;
+  R.Spp = rb + s->o_Spp; R.Spb = rb + s->o_Spb; R.Sbb = rb + s->o_Sbb;
+  R.Fpp = with_F ? rb + s->o_Fpp : nullptr; R.Fbb = with_F ? rb + s->o_Fbb : nullptr;
+  R.g = rb + s->o_g; R.diagF = rb + s->o_diagF; R.rhs = rb + s->o_rhs;
+  R.pairtab = s->pairtab.p; R.nb = nb; R.npc = s->npc; R.B = s->B; R.nf = s->nf;
+  s->A.row_ptr = s->row_ptr.p; s->A.col = s->col.p; s->A.slot = s->slot.p; s->A.nb = nb;
+  // launch geometry: as many warps per CTA as shared memory allows, persistent grid
+  size_t pw = build_smem_per_warp(s->maxposes, s->B, s->maxdz, s->vwmax);
+  int dev_smem = 0;
+  MVBA_CUDA(cudaDeviceGetAttribute(&dev_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device));
+  if (pw > (size_t)dev_smem) return fail(MVBA_EINVAL, "mvba: a track touches too many parameter columns for one warp's shared memory");
+  s->wpb_build = (int)std::max<size_t>(1, std::min<size_t>(8, (size_t)dev_smem / 2 / pw));
+  s->smem_build = pw * s->wpb_build;
+  MVBA_CUDA(cudaFuncSetAttribute(build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_build));
+  size_t pwb = (sizeof(Stash) * MVBA_CHUNK / 8 + (size_t)MVBA_CHUNK * 2 * s->maxdz + (size_t)s->maxitems * 15) * 8;
+  if (pwb > (size_t)dev_smem) return fail(MVBA_EINVAL, "mvba: a track has too many residual blocks for one warp's shared memory");
+  s->wpb_backsub = (int)std::max<size_t>(1, std::min<size_t>(8, (size_t)dev_smem / 2 / pwb));
+  s->smem_backsub = pwb * s->wpb_backsub;
+  MVBA_CUDA(cudaFuncSetAttribute(backsub_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_backsub));
+  int occ = 1;
+  MVBA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, build_kernel, 32 * s->wpb_build, s->smem_build));
+  s->grid_build = std::max(1, std::min((v.P + s->wpb_build - 1) / s->wpb_build, h->sm_count * std::max(occ, 1)));
+  MVBA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, backsub_kernel, 32 * s->wpb_backsub, s->smem_backsub));
+  s->grid_backsub = std::max(1, std::min((v.P + s->wpb_backsub - 1) / s->wpb_backsub, h->sm_count * std::max(occ, 1)));
+  return MVBA_OK;
+}
+
+}  // namespace mvba
+
+#include "solver_loop.cuh"
