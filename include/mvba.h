@@ -127,8 +127,10 @@ typedef struct {
   int32_t jacobi_scaling;             /* 1                                                  */
   int32_t linear_solver;              /* 0 = PCG on the reduced camera system (ITERATIVE_SCHUR),
                                          1 = dense FP64 tensor-core Cholesky of the reduced system */
-  int32_t preconditioner;             /* 0 = block Jacobi of F'F+D (Ceres JACOBI, the reference's
-                                         default), 1 = block Jacobi of S (SCHUR_JACOBI)     */
+  int32_t preconditioner;             /* 0 = block Jacobi of F'F+D, one block per parameter block (Ceres
+                                         JACOBI, the reference's default); 1 = block Jacobi of S, same
+                                         partition (SCHUR_JACOBI); 2 = block Jacobi of S with all shared
+                                         per-sensor blocks (rig, intrinsics, depth) as one dense block */
   int32_t verbose;                    /* minimizer_progress_to_stdout                        */
 } mvba_solve_options;
 

@@ -72,12 +72,20 @@ __global__ void precond_pose_kernel(Reduced S, int use_F, double* __restrict__ M
 }
 
 // One CTA: mirror Sbb, then invert the border block (B x B, SPD) by Gauss-Jordan in global memory.
-__global__ void __launch_bounds__(256) precond_border_kernel(Reduced S, int use_F, double* __restrict__ Minv, double* __restrict__ work) {
+// blk: parameter-block id of each border column; entries coupling different blocks are dropped so that
+// the preconditioner has Ceres' block-diagonal partition (null: keep the border dense).
+__global__ void __launch_bounds__(256) precond_border_kernel(Reduced S, int use_F, const int32_t* __restrict__ blk,
+                                                              double* __restrict__ Minv, double* __restrict__ work) {
   const int B = S.B, tid = threadIdx.x, nt = blockDim.x;
   for (int i = tid; i < B * B; i += nt) { int r = i / B, c = i - r * B; if (c < r) S.Sbb[i] = S.Sbb[(size_t)c * B + r]; }
   __syncthreads();
   const double* src = use_F ? S.Fbb : S.Sbb;
-  for (int i = tid; i < B * B; i += nt) { int r = i / B, c = i - r * B; work[i] = (c >= r) ? src[i] : src[(size_t)c * B + r]; Minv[i] = (r == c) ? 1.0 : 0.0; }
+  for (int i = tid; i < B * B; i += nt) {
+    int r = i / B, c = i - r * B;
+    double val = (c >= r) ? src[i] : src[(size_t)c * B + r];
+    if (blk && blk[r] != blk[c]) val = 0.0;
+    work[i] = val; Minv[i] = (r == c) ? 1.0 : 0.0;
+  }
   __syncthreads();
   __shared__ double piv_s;
   for (int k = 0; k < B; k++) {

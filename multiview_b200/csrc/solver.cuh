@@ -67,7 +67,7 @@ struct Solver {
   int nb = 0, npc = 0, B = 0, nf = 0;
   int64_t nslots = 0, nnzb = 0;
   int maxposes = 1, maxitems = 1, maxdz = 1, vwmax = MVBA_VPOSE + 4;
-  DBuf<int32_t> pairtab, row_ptr, col, slot, xcol;
+  DBuf<int32_t> pairtab, row_ptr, col, slot, xcol, border_blk;
   DBuf<double> red;  // [Spp | Spb | Sbb | Fpp | Fbb | g | diagF | rhs | cost]  (one allreduce)
   size_t o_Spp = 0, o_Spb = 0, o_Sbb = 0, o_Fpp = 0, o_Fbb = 0, o_g = 0, o_diagF = 0, o_rhs = 0, o_cost = 0, red_n = 0;
   DBuf<double> Dsq, Mpp, Mbb, work, jscale_f, jscale_e, Hinv, ge, diagE, lo, hi;
@@ -147,6 +147,17 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
   s->maxdz = maxdz; s->vwmax = vw;
   MVBA_CUDA(s->pairtab.upload(pairtab)); MVBA_CUDA(s->row_ptr.upload(row_ptr)); MVBA_CUDA(s->col.upload(col)); MVBA_CUDA(s->slot.upload(slot));
   MVBA_CUDA(s->xcol.upload(h->h_xcol));
+  {  // parameter-block id of every border column (Ceres' block-Jacobi partition)
+    std::vector<int32_t> blk(std::max(s->B, 1), 0);
+    int id = 0;
+    for (int t = 0; t < v.T; t++) {
+      const SensorDev& sd = v.sens[t];
+      const int c0[7] = {sd.c_rig, sd.c_off, sd.c_focal, sd.c_center, sd.c_dist, sd.c_d2i, sd.c_scale};
+      const int w[7] = {7, 1, 1, 2, sd.nd, v.nd2i, 1};
+      for (int k = 0; k < 7; k++) if (c0[k] >= 0) { for (int j = 0; j < w[k]; j++) blk[c0[k] - s->npc + j] = id; id++; }
+    }
+    MVBA_CUDA(s->border_blk.upload(blk));
+  }
   if (h->bounded) { MVBA_CUDA(s->lo.upload(h->h_lo)); MVBA_CUDA(s->hi.upload(h->h_hi)); }
   // one contiguous buffer for everything that is summed across ranks
   size_t o = 0;

@@ -140,7 +140,7 @@ inline int solver_solve(mvba_problem* h, const mvba_solve_options& o, mvba_summa
     if (s->nf) {
       damp_kernel<<<(s->nf + tb - 1) / tb, tb, 0, h->stream>>>(s->R, radius, o.min_lm_diagonal, o.max_lm_diagonal, s->Dsq.p);
       if (s->nb) precond_pose_kernel<<<(s->nb + 63) / 64, 64, 0, h->stream>>>(s->R, s->with_F ? 1 : 0, s->Mpp.p);
-      if (s->B) precond_border_kernel<<<1, 256, 0, h->stream>>>(s->R, s->with_F ? 1 : 0, s->Mbb.p, s->work.p);
+      if (s->B) precond_border_kernel<<<1, 256, 0, h->stream>>>(s->R, s->with_F ? 1 : 0, o.preconditioner == 2 ? nullptr : s->border_blk.p, s->Mbb.p, s->work.p);
       h->launches += 3;
     }
     tm.end();
