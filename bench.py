@@ -1,0 +1,246 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the B200-native bundle-adjustment path.
+
+A "step" is ONE Levenberg-Marquardt iteration of rig_calibrator's solve (1 fused residual+Jacobian+
+Schur build, 1 PCG solve of the reduced camera system, 1 back-substitution, 1 candidate-cost pass,
+accept/reject) on the synthetic config named in config.workload (BASELINE.json config 5 by default:
+2000 ref frames x 1M landmarks x 8 obs/track, 3-sensor rig).
+
+  value : LM iterations/s, parameters resident in HBM (CUDA events around the LM loop, max over ranks)
+  e2e   : LM iterations/s through the C ABI call mvba_solve() with HOST parameter arrays
+          (host->device upload and device->host write-back inside the timed region)
+  roofline / cpu_baseline : see DESIGN.md "Measurement"
+
+`--impl reference` times the reference's CPU algorithm (the oracle restatement of the functors +
+Ceres-1.14-style numeric-diff LM; Ceres itself is not available on this box) on a bounded sample.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", type=int, default=5)
+    ap.add_argument("--scale", type=float, default=1.0, help="shrink the workload (debug only; invalidates the number)")
+    ap.add_argument("--cpu-sample", type=float, default=0.1, help="fraction of the workload timed on the CPU")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--preconditioner", type=int, default=0)
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+            except Exception:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[4:8]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def algorithmic_bytes(pr):
+    """bytes the unfused residual/Jacobian + J'J/Schur kernels must move for one build."""
+    T = len(pr.sensors)
+    free_pose = 7 if pr.float_poses is not None and pr.float_poses[0] else 0
+    sens = pr.cam_sensor[pr.cid]
+    direct = pr.cam_beg[pr.cid] == pr.cam_end[pr.cid]
+    pf = np.full(pr.num_obs, 3.0)  # xyz
+    pf += free_pose * np.where(direct, 1, 2)
+    for t in range(T):
+        m = sens == t
+        extra = 0
+        if pr.float_rig is not None and pr.float_rig[t] and t != 0: extra += 7
+        if pr.float_focal is not None and pr.float_focal[t]: extra += 1
+        if pr.float_center is not None and pr.float_center[t]: extra += 2
+        if pr.float_dist is not None and pr.float_dist[t]: extra += pr.sensors[t].nd
+        pf[m] += extra
+    N, P = pr.num_obs, pr.num_landmarks
+    k = N / max(P, 1)
+    b_rj = float(np.sum(32 + 16 * pf + 24 / k))
+    b_schur = float(np.sum(16 * pf + 16) + 72 * P)
+    return b_rj, b_schur, float(pf.mean())
+
+
+def cpu_baseline(pr_full, frac, jac_mode=0, iters=3):
+    """Times the oracle's Ceres-style LM (numeric-diff Jacobians as the reference incurs them) on a
+    bounded sample and scales to the full workload by observation count."""
+    from multiview_b200 import _abi, synth
+    lib = C.CDLL(os.path.join(ROOT, "oracle", "liboracle.so"))
+    lib.oracle_max_threads.restype = C.c_int
+    cores = int(lib.oracle_max_threads())
+    pr = synth.config(int(pr_full.name[6]), scale=frac)
+    b = _abi.Binding(lib, "oracle_", pr)
+    t0 = time.time()
+    s, _ = b.solve(_abi.default_options(max_num_iterations=iters), jac_mode=jac_mode, num_threads=cores)
+    dt = time.time() - t0
+    b.close()
+    it_per_s_sample = s.num_iterations / dt
+    ratio = pr.num_obs / pr_full.num_obs
+    return {"value": it_per_s_sample * ratio, "unit": "LM iterations/s", "cores": cores, "kind": "port",
+            "sample": f"{pr.name} at scale {frac:g}: {pr.num_obs} observations / {pr.num_landmarks} landmarks, {s.num_iterations} LM iterations in "
+                      f"{dt:.2f} s ({'Ceres-rule numeric-diff' if jac_mode == 0 else 'forward-mode dual'} Jacobians, OpenMP {cores} threads); "
+                      f"scaled to the full workload by observation count x{ratio:.3g}",
+            "sample_seconds": dt, "sample_lm_iterations_per_s": it_per_s_sample}
+
+
+def run_reference(args):
+    """The reference arm: the reference's own CPU algorithm (oracle port, all host threads)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from multiview_b200 import synth
+    # shape of the full workload without materialising 8M observations
+    full = {1: (10000, 4), 2: (60000, 5), 3: (20000, 5), 4: (200000, 6), 5: (1000000, 8)}[args.config]
+    class _Full: pass
+    pf = _Full(); pf.name = f"config{args.config}"; pf.num_obs = int(full[0] * full[1] * args.scale)
+    pf.name = synth.config(args.config, scale=1e-4).name
+    steps = max(1, args.steps)
+    t0 = time.time()
+    cb = cpu_baseline(pf, args.cpu_sample, jac_mode=0, iters=args.warmup + steps)
+    value = cb["value"]
+    line = {"metric": "LM iterations/s", "value": value, "unit": "LM iterations/s", "n_gpus": args.gpus, "steps": steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 / value if value > 0 else None, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic", "impl": "reference",
+            "config": {"workload": pf.name, "observations": pf.num_obs, "note": "Ceres-equivalent CPU restatement (Ceres itself unavailable on this box)"},
+            "cpu_baseline": dict(cb, value=value),
+            "e2e": {"value": value, "unit": "LM iterations/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0, "wall_s": time.time() - t0}
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from multiview_b200 import _abi, synth
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    lib = _abi.load_product()
+    pr_full = synth.config(args.config, scale=args.scale)
+    pr = pr_full.shard(rank, world) if world > 1 else pr_full
+    g = _abi.Binding(lib, "mvba_", pr, device=local)
+    if world > 1:
+        idbuf = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            raw = (C.c_uint8 * 128)()
+            assert lib.mvba_nccl_unique_id(raw) == 0
+            idbuf.copy_(torch.tensor(list(raw), dtype=torch.uint8))
+        dist.broadcast(idbuf, 0)
+        raw = (C.c_uint8 * 128)(*idbuf.cpu().tolist())
+        g._ck(lib.mvba_comm_init(g.h, rank, world, raw))
+    snap = pr.snapshot()
+    opts = dict(preconditioner=args.preconditioner)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # warm-up: W LM iterations from the initial point (also builds the reduced-system structure)
+    s_w, _ = g.solve(_abi.default_options(max_num_iterations=max(args.warmup, 3), **opts))
+    pr.restore(snap)
+    sampler = ClockSampler(local)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    t0 = time.perf_counter()
+    s, log = g.solve(_abi.default_options(max_num_iterations=args.steps, **opts))
+    barrier()
+    wall = time.perf_counter() - t0
+    clocks = sampler.stop() if rank == 0 else None
+    steps = s.num_iterations
+    times = torch.tensor([s.seconds_device, wall, s.seconds_build_kernel, s.seconds_build, s.seconds_linear, s.seconds_update], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(times, op=dist.ReduceOp.MAX)
+    t_dev, t_wall, t_bk, t_build, t_lin, t_upd = times.tolist()
+    # roofline leg: the fused build kernel, CUDA events around its launches inside the timed solve
+    b_rj, b_schur, pfree = algorithmic_bytes(pr)
+    per_launch_s = t_bk / max(s.num_build_launches, 1)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    achieved = (b_rj + b_schur) / per_launch_s / 1e9
+    h2d = sum(a.nbytes for a in pr.param_arrays().values()); d2h = h2d
+    line = {"metric": "LM iterations/s", "value": steps / t_dev, "unit": "LM iterations/s", "n_gpus": world, "steps": steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": 1e3 * t_dev / steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": pr_full.name, "ref_frames": len(pr_full.ref_stamps), "cameras": len(pr_full.cam_sensor), "landmarks": pr_full.num_landmarks,
+                       "observations": pr_full.num_obs, "parallelism": f"landmark-sharded x{world}", "l2": "inputs (>= 128 MB of observations + landmarks per pass at full size) exceed L2",
+                       "scale": args.scale, "preconditioner": args.preconditioner, "mean_free_params_per_obs": pfree},
+            "evals_per_s": pr_full.num_obs * (s.num_jacobian_evals) / t_dev,
+            "e2e": {"value": steps / t_wall, "unit": "LM iterations/s", "h2d_bytes_per_step": h2d / steps, "d2h_bytes_per_step": d2h / steps,
+                    "note": "mvba_solve() on host parameter arrays; upload + write-back amortised over the steps of one solve"},
+            "gpu_launches": int(s.num_kernel_launches),
+            "phases_s": {"build": t_build, "build_kernel": t_bk, "linear": t_lin, "update": t_upd, "device_total": t_dev},
+            "solve": {"initial_cost": s.initial_cost, "final_cost": s.final_cost, "successful_steps": s.num_successful_steps,
+                      "pcg_iterations": s.num_linear_iterations, "jacobian_evals": s.num_jacobian_evals},
+            "roofline": {"bound": "hbm", "kernel": "build_kernel (fused residual+Jacobian+J'J+Schur)", "achieved": achieved, "peak": peak,
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6.65 TB/s", "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "algorithmic_bytes_per_launch": b_rj + b_schur, "launch_ms": 1e3 * per_launch_s, "launches": s.num_build_launches},
+            "clocks": clocks}
+    if rank == 0:
+        if not args.no_cpu_baseline and world == 1:
+            line["cpu_baseline"] = cpu_baseline(pr_full, args.cpu_sample)
+        print(json.dumps(line), flush=True)
+    g.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

@@ -157,6 +157,9 @@ typedef struct {
   double seconds_update;         /* CUDA-event time in back-substitution + candidate cost   */
   double final_gradient_max_norm;
   double final_radius;
+  double seconds_build_kernel;   /* CUDA-event time inside the fused build kernel launches only */
+  int32_t num_build_launches;    /* launches of the fused build kernel (incl. the column-norm pass) */
+  int32_t reserved;
 } mvba_summary;
 
 /* Per-iteration log, Ceres' progress table (minimizer_progress_to_stdout). */

@@ -49,7 +49,8 @@ class Summary(C.Structure):
                 ("num_jacobian_evals", C.c_int32), ("num_residual_evals", C.c_int32), ("num_kernel_launches", C.c_int64),
                 ("seconds_total", C.c_double), ("seconds_device", C.c_double), ("seconds_build", C.c_double),
                 ("seconds_linear", C.c_double), ("seconds_update", C.c_double), ("final_gradient_max_norm", C.c_double),
-                ("final_radius", C.c_double)]
+                ("final_radius", C.c_double), ("seconds_build_kernel", C.c_double), ("num_build_launches", C.c_int32),
+                ("reserved", C.c_int32)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

@@ -63,7 +63,10 @@ inline int allreduce(mvba_problem* h, void* buf, size_t n, int dtype, int op) {
   return rc ? fail(MVBA_ENCCL, std::string("ncclAllReduce: ") + nc.GetErrorString(rc)) : MVBA_OK;
 }
 
+struct Timers;
 struct Solver {
+  Timers* tm = nullptr;
+  int build_launches = 0;
   int nb = 0, npc = 0, B = 0, nf = 0;
   int64_t nslots = 0, nnzb = 0;
   int maxposes = 1, maxitems = 1, maxdz = 1, vwmax = MVBA_VPOSE + 4;

@@ -4,16 +4,17 @@
 namespace mvba {
 
 struct Timers {
-  std::vector<cudaEvent_t> ev;
-  std::vector<int> tag;  // phase of interval [2k, 2k+1]
+  struct Iv { cudaEvent_t a, b; int phase; };
+  std::vector<Iv> iv;
+  std::vector<size_t> open;
   cudaStream_t s;
   explicit Timers(cudaStream_t st) : s(st) {}
-  ~Timers() { for (auto e : ev) cudaEventDestroy(e); }
-  void begin(int phase) { cudaEvent_t e; cudaEventCreate(&e); cudaEventRecord(e, s); ev.push_back(e); tag.push_back(phase); }
-  void end() { cudaEvent_t e; cudaEventCreate(&e); cudaEventRecord(e, s); ev.push_back(e); }
+  ~Timers() { for (auto& i : iv) { cudaEventDestroy(i.a); if (i.b) cudaEventDestroy(i.b); } }
+  void begin(int phase) { Iv i{nullptr, nullptr, phase}; cudaEventCreate(&i.a); cudaEventRecord(i.a, s); iv.push_back(i); open.push_back(iv.size() - 1); }
+  void end() { Iv& i = iv[open.back()]; open.pop_back(); cudaEventCreate(&i.b); cudaEventRecord(i.b, s); }
   double total(int phase) {
     double t = 0;
-    for (size_t k = 0; k + 1 < ev.size(); k += 2) if (tag[k / 2] == phase) { float ms = 0; cudaEventElapsedTime(&ms, ev[k], ev[k + 1]); t += ms; }
+    for (auto& i : iv) if (i.phase == phase && i.b) { float ms = 0; cudaEventElapsedTime(&ms, i.a, i.b); t += ms; }
     return t * 1e-3;
   }
 };
@@ -31,8 +32,10 @@ inline int run_build(mvba_problem* h, const mvba_solve_options& o, double radius
   a.Hinv = s->Hinv.p; a.ge = s->ge.p; a.diagE = s->diagE.p; a.cost = s->red.p + s->o_cost;
   a.mode = mode; a.maxposes = s->maxposes; a.maxdz = s->maxdz; a.vwmax = s->vwmax;
   if (v.P > 0) {
+    if (s->tm) s->tm->begin(9);
     build_kernel<<<s->grid_build, 32 * s->wpb_build, s->smem_build, h->stream>>>(v, a, s->R);
-    h->launches++;
+    if (s->tm) s->tm->end();
+    h->launches++; s->build_launches++;
   }
   MVBA_CUDA(cudaGetLastError());
   return allreduce(h, s->red.p, s->red_n, 8, 0);
@@ -107,6 +110,7 @@ inline int solver_solve(mvba_problem* h, const mvba_solve_options& o, mvba_summa
   const double init[2] = {o.initial_trust_region_radius, 2.0};
   MVBA_CUDA(cudaMemcpyAsync(s->lm.p + LM_RADIUS, init, 2 * sizeof(double), cudaMemcpyHostToDevice, h->stream));
   Timers tm(h->stream);
+  s->tm = &tm; s->build_launches = 0;
   enum { PH_ALL = 0, PH_BUILD = 1, PH_LINEAR = 2, PH_UPDATE = 3 };
   cudaEvent_t e_all0, e_all1;
   MVBA_CUDA(cudaEventCreate(&e_all0)); MVBA_CUDA(cudaEventCreate(&e_all1));
@@ -210,6 +214,7 @@ inline int solver_solve(mvba_problem* h, const mvba_solve_options& o, mvba_summa
   S->num_kernel_launches = h->launches - launches0;
   S->seconds_device = ms_all * 1e-3; S->seconds_build = tm.total(PH_BUILD); S->seconds_linear = tm.total(PH_LINEAR); S->seconds_update = tm.total(PH_UPDATE);
   S->final_gradient_max_norm = gmax; S->final_radius = radius;
+  S->seconds_build_kernel = tm.total(9); S->num_build_launches = s->build_launches; s->tm = nullptr;
   S->seconds_total = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
   return MVBA_OK;
 }
@@ -219,6 +224,7 @@ inline int solver_bench_build(mvba_problem* h, int repeats, float* ms_total) {
   mvba_solve_options o; mvba_solve_options_init(&o);
   int rc = solver_prepare(h, false); if (rc) return rc;
   Solver* s = h->solver;
+  s->tm = nullptr;
   rc = run_build(h, o, o.initial_trust_region_radius, 1, false); if (rc) return rc;
   const int tb = 256; const int64_t ne = 3 * (int64_t)h->view.P;
   if (s->nf) jscale_kernel<<<(s->nf + tb - 1) / tb, tb, 0, h->stream>>>(s->nf, s->R.diagF, s->jscale_f.p);
