@@ -1,8 +1,10 @@
-// kernels_build.cuh -- fused normal-equation build: per track (one warp) residuals + analytic
-// Jacobians are evaluated in registers, J'J / J'r blocks are reduced in shared memory, the 3x3
-// landmark block is inverted and the track is Schur-eliminated straight into the reduced camera
-// system.  Jacobians never touch HBM.  (north-star kernels (a)+(b); Ceres 1.14 equivalent:
-// Evaluate + Corrector + ImplicitSchurComplement::Init, made explicit.)
+// kernels_build.cuh -- pass B of the normal-equation build, generic version: one warp per track.
+// Residuals + analytic Jacobians are evaluated in registers, G = F'E and the 3x3 landmark block E'E
+// are reduced in shared memory, the landmark block is inverted and the track is Schur-eliminated
+// straight into the reduced camera system with atomics.  Jacobians never touch HBM.  This kernel
+// takes any track (any number of poses / columns); kernels_tile.cuh is the fast path for tracks
+// whose poses fall in a narrow window.  F'F and F'r come from pass A (kernels_camera.cuh).
+// (north-star kernel (b); Ceres 1.14 equivalent: SchurEliminator::Eliminate, made explicit.)
 #pragma once
 #include "items.cuh"
 
@@ -36,6 +38,8 @@ struct BuildArgs {
   int maxposes;   // per-track capacity of the local pose list
   int maxdz;      // max nd_nz
   int vwmax;      // max virtual width
+  const int32_t* trk_list;  // tracks to process (null: all of [0, ntrk))
+  int ntrk;
 };
 
 __device__ __forceinline__ void addS(const Reduced& S, int g1, int g2, double val) {
@@ -75,12 +79,11 @@ __device__ __forceinline__ void tri_decode(int idx, int& i, int& j) {
 }
 
 // Dynamic shared memory per warp (doubles first, then ints):
-//   stash[CHUNK] | Jd[CHUNK][2][maxdz] | Jv[3][vwmax] | G[nloc][3] | Y[nloc][3] | gl[nloc] | dl[nloc]
-//   | lcol[nloc] (int) | gcv[vwmax] (int) | act[vwmax] (int) | lposes[maxposes] (int)
+//   stash[CHUNK] | Jd[CHUNK][2][maxdz] | G[nloc][3] | Y[nloc][3] | lcol[nloc] (int) | lposes[maxposes] (int)
 __host__ __device__ inline size_t build_smem_per_warp(int maxposes, int B, int maxdz, int vwmax) {
   size_t nloc = (size_t)7 * maxposes + B;
-  size_t d = sizeof(Stash) * MVBA_CHUNK / 8 + (size_t)MVBA_CHUNK * 2 * maxdz + 3 * (size_t)vwmax + nloc * 8;
-  size_t i = nloc + 2 * (size_t)vwmax + maxposes;
+  size_t d = sizeof(Stash) * MVBA_CHUNK / 8 + (size_t)MVBA_CHUNK * 2 * maxdz + nloc * 6;
+  size_t i = nloc + maxposes;
   return d * 8 + ((i * 4 + 7) / 8) * 8;
 }
 
@@ -92,19 +95,15 @@ __global__ void __launch_bounds__(256) build_kernel(View v, BuildArgs a, Reduced
   double* base = smem_d + per_warp * wib;
   Stash* stash = reinterpret_cast<Stash*>(base);
   double* Jd = base + sizeof(Stash) * MVBA_CHUNK / 8;
-  double* Jv = Jd + (size_t)MVBA_CHUNK * 2 * a.maxdz;
-  double* G = Jv + 3 * (size_t)a.vwmax;
+  double* G = Jd + (size_t)MVBA_CHUNK * 2 * a.maxdz;
   double* Y = G + 3 * (size_t)nlocmax;
-  double* gl = Y + 3 * (size_t)nlocmax;
-  double* dl = gl + nlocmax;
-  int* lcol = reinterpret_cast<int*>(dl + nlocmax);
-  int* gcv = lcol + nlocmax;
-  int* act = gcv + a.vwmax;
-  int* lposes = act + a.vwmax;
+  int* lcol = reinterpret_cast<int*>(Y + 3 * (size_t)nlocmax);
+  int* lposes = lcol + nlocmax;
   const int B = S.B;
   double cost_acc = 0;
 
-  for (int p = blockIdx.x * wpb + wib; p < v.P; p += gridDim.x * wpb) {
+  for (int ti = blockIdx.x * wpb + wib; ti < a.ntrk; ti += gridDim.x * wpb) {
+    const int p = a.trk_list ? a.trk_list[ti] : ti;
     const int64_t o0 = v.trk_obs0[p], o1 = v.trk_obs0[p + 1];
     const int64_t d0 = v.trk_dtri0[p], d1 = v.trk_dtri0[p + 1];
     const int64_t m0 = v.trk_dmesh0[p], m1 = v.trk_dmesh0[p + 1];
@@ -115,7 +114,7 @@ __global__ void __launch_bounds__(256) build_kernel(View v, BuildArgs a, Reduced
     if (nitems == 0) continue;
     // local system starts with the border columns
     int npl = 0;
-    for (int li = lane; li < nlocmax; li += 32) { G[3 * li] = G[3 * li + 1] = G[3 * li + 2] = 0; gl[li] = 0; dl[li] = 0; lcol[li] = li < B ? S.npc + li : -1; }
+    for (int li = lane; li < nlocmax; li += 32) { G[3 * li] = G[3 * li + 1] = G[3 * li + 2] = 0; lcol[li] = li < B ? S.npc + li : -1; }
     double H[6] = {0, 0, 0, 0, 0, 0}, gE[3] = {0, 0, 0};
     double se[3] = {1, 1, 1};
     if (a.jscale_e) { se[0] = a.jscale_e[3 * (size_t)p]; se[1] = a.jscale_e[3 * (size_t)p + 1]; se[2] = a.jscale_e[3 * (size_t)p + 2]; }
@@ -151,7 +150,8 @@ __global__ void __launch_bounds__(256) build_kernel(View v, BuildArgs a, Reduced
         }
       }
       __syncwarp();
-      // ---- phase 2: the warp walks the chunk's items, lanes over Jacobian columns ----
+      if (a.mode == 1) continue;  // column norms: only diag(E'E) is needed here
+      // ---- phase 2: the warp walks the chunk's items, lanes over Jacobian columns: G += J_f' E ----
       for (int j = 0; j < cnt; j++) {
         const Stash& st = stash[j];
         if (st.kind == MVBA_BLOCK_MESH_TRI || st.kind == MVBA_BLOCK_TRI) continue;  // no f columns
@@ -185,7 +185,6 @@ __global__ void __launch_bounds__(256) build_kernel(View v, BuildArgs a, Reduced
         }
         const int vw = item_vwidth(v, it);
         const double* jd0 = Jd + (size_t)j * 2 * a.maxdz;
-        int na = 0;
         for (int v0 = 0; v0 < vw; v0 += 32) {
           int vc = v0 + lane;
           int gc = -1;
@@ -195,33 +194,12 @@ __global__ void __launch_bounds__(256) build_kernel(View v, BuildArgs a, Reduced
             item_jcol(v, it, a.tab, a.dtab, vc, jd0, jd0 + a.maxdz, col);
             double sc = st.sr * (a.jscale_f ? a.jscale_f[gc] : 1.0);
             int li = gc >= S.npc ? gc - S.npc : B + 7 * (vc < 7 ? lp[0] : lp[1]) + (vc < 7 ? vc : vc - 7);
-            double g0 = 0, g1 = 0, g2 = 0, gr = 0, dd = 0;
+            double g0 = 0, g1 = 0, g2 = 0;
             for (int r = 0; r < st.nr; r++) {
               double jv = col[r] * sc;
-              Jv[r * a.vwmax + vc] = jv;
               g0 += jv * st.E[3 * r]; g1 += jv * st.E[3 * r + 1]; g2 += jv * st.E[3 * r + 2];
-              gr += jv * st.r[r]; dd += jv * jv;
             }
-            G[3 * li] += g0; G[3 * li + 1] += g1; G[3 * li + 2] += g2; gl[li] += gr; dl[li] += dd;
-          }
-          if (vc < vw) gcv[vc] = gc;
-          unsigned mk = __ballot_sync(0xffffffffu, gc >= 0);
-          if (gc >= 0) act[na + __popc(mk & ((1u << lane) - 1))] = vc;
-          na += __popc(mk);
-        }
-        __syncwarp();
-        if (a.mode == 0) {
-          const int np = na * (na + 1) / 2;
-          for (int idx = lane; idx < np; idx += 32) {
-            int i1, i2;
-            tri_decode(idx, i1, i2);
-            int v1 = act[i1], v2 = act[i2];
-            double val = 0;
-            for (int r = 0; r < st.nr; r++) val += Jv[r * a.vwmax + v1] * Jv[r * a.vwmax + v2];
-            if (val != 0.0) {
-              addS(S, gcv[v1], gcv[v2], val);
-              if (S.Fpp) addFdiag(S, gcv[v1], gcv[v2], val);
-            }
+            G[3 * li] += g0; G[3 * li + 1] += g1; G[3 * li + 2] += g2;
           }
         }
         __syncwarp();
@@ -235,7 +213,6 @@ __global__ void __launch_bounds__(256) build_kernel(View v, BuildArgs a, Reduced
     const int nloc = B + 7 * npl;
     if (a.mode == 1) {
       if (lane == 0) { a.diagE[3 * (size_t)p] = H[0]; a.diagE[3 * (size_t)p + 1] = H[3]; a.diagE[3 * (size_t)p + 2] = H[5]; }
-      for (int li = lane; li < nloc; li += 32) if (dl[li] != 0.0) atomicAdd(S.diagF + lcol[li], dl[li]);
       __syncwarp();
       continue;
     }
@@ -253,12 +230,7 @@ __global__ void __launch_bounds__(256) build_kernel(View v, BuildArgs a, Reduced
       Y[3 * li] = Hi[0] * g0 + Hi[1] * g1 + Hi[2] * g2;
       Y[3 * li + 1] = Hi[1] * g0 + Hi[3] * g1 + Hi[4] * g2;
       Y[3 * li + 2] = Hi[2] * g0 + Hi[4] * g1 + Hi[5] * g2;
-      int gc = lcol[li];
-      if (gl[li] != 0.0 || dl[li] != 0.0) {
-        atomicAdd(S.g + gc, gl[li]);
-        atomicAdd(S.diagF + gc, dl[li]);
-        atomicAdd(S.rhs + gc, gl[li] - (g0 * ve[0] + g1 * ve[1] + g2 * ve[2]));
-      }
+      if (g0 != 0.0 || g1 != 0.0 || g2 != 0.0) atomicAdd(S.rhs + lcol[li], -(g0 * ve[0] + g1 * ve[1] + g2 * ve[2]));
     }
     __syncwarp();
     // ---- Schur elimination: S -= G Hinv G' over the track's local columns ----

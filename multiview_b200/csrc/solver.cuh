@@ -10,6 +10,7 @@
 
 #include "handle.cuh"
 #include "kernels_lm.cuh"
+#include "kernels_camera.cuh"
 
 namespace mvba {
 
@@ -81,6 +82,10 @@ struct Solver {
   size_t smem_build = 0, smem_backsub = 0;
   int wpb_build = 8, wpb_backsub = 8, grid_build = 1, grid_backsub = 1;
   bool with_F = false;
+  // pass A (camera-major F'F): block codes grouped by image, split into chunks
+  DBuf<int32_t> citems, chunk_cam, chunk_beg;
+  int nchunks = 0, cam_batch = 0, cam_ldj = 0, grid_cam = 1;
+  size_t smem_cam = 0;
   Reduced R{};
   Bsr A{};
 };
@@ -187,6 +192,41 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
   R.g = rb + s->o_g; R.diagF = rb + s->o_diagF; R.rhs = rb + s->o_rhs;
   R.pairtab = s->pairtab.p; R.nb = nb; R.npc = s->npc; R.B = s->B; R.nf = s->nf;
   s->A.row_ptr = s->row_ptr.p; s->A.col = s->col.p; s->A.slot = s->slot.p; s->A.nb = nb;
+  {  // ---- pass A: residual blocks with f columns grouped by camera image (counting sort), chunked ----
+    const int64_t nit = v.N + v.n_dtri + v.n_dmesh;
+    if (nit >= ((int64_t)1 << 31)) return fail(MVBA_EINVAL, "mvba: more than 2^31 residual blocks on one device");
+    std::vector<int32_t> cnt(v.C + 1, 0);
+    auto cam_of = [&](int64_t code) -> int {
+      if (code < v.N) return h->ocid[code];
+      if (code < v.N + v.n_dtri) return h->ocid[h->h_dtri_obs[code - v.N]];
+      return h->ocid[h->h_dmesh_obs[code - v.N - v.n_dtri]];
+    };
+    for (int64_t q = 0; q < nit; q++) cnt[cam_of(q) + 1]++;
+    for (int c = 0; c < v.C; c++) cnt[c + 1] += cnt[c];
+    std::vector<int32_t> items((size_t)nit), fill(cnt.begin(), cnt.end() - 1);
+    for (int64_t q = 0; q < nit; q++) items[fill[cam_of(q)]++] = (int32_t)q;  // codes ascend inside an image
+    // widest image: active columns + r, padded to blocks of 4
+    int maxact = 0;
+    for (int t = 0; t < v.T; t++) {
+      const SensorDev& sd = v.sens[t];
+      int n = (v.npose_cols ? 14 : 0) + (sd.c_rig >= 0 ? 7 : 0) + (sd.c_off >= 0) + (sd.c_focal >= 0) + (sd.c_center >= 0 ? 2 : 0) +
+              (sd.c_dist >= 0 ? sd.nd_nz : 0) + (sd.c_d2i >= 0 ? v.nd2i : 0) + (sd.c_scale >= 0);
+      maxact = std::max(maxact, n);
+    }
+    if (maxact + 1 > MVBA_CAM_MAXACT) return fail(MVBA_EINVAL, "mvba: one image touches more than 87 free non-landmark columns");
+    s->cam_ldj = ((maxact + 1 + 3) / 4) * 4;
+    const int64_t target = std::max<int64_t>(256, std::min<int64_t>(4096, nit / std::max(1, 4 * h->sm_count)));
+    std::vector<int32_t> ccam, cbeg;
+    for (int c = 0; c < v.C; c++) {
+      int n = cnt[c + 1] - cnt[c];
+      if (n == 0) continue;
+      int parts = (int)((n + target - 1) / target);
+      for (int k = 0; k < parts; k++) { ccam.push_back(c); cbeg.push_back(cnt[c] + (int)((int64_t)n * k / parts)); }
+    }
+    cbeg.push_back((int32_t)nit);
+    s->nchunks = (int)ccam.size();
+    MVBA_CUDA(s->citems.upload(items)); MVBA_CUDA(s->chunk_cam.upload(ccam)); MVBA_CUDA(s->chunk_beg.upload(cbeg));
+  }
   // launch geometry: as many warps per CTA as shared memory allows, persistent grid
   size_t pw = build_smem_per_warp(s->maxposes, s->B, s->maxdz, s->vwmax);
   int dev_smem = 0;
@@ -200,6 +240,18 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
   s->wpb_backsub = (int)std::max<size_t>(1, std::min<size_t>(8, (size_t)dev_smem / 2 / pwb));
   s->smem_backsub = pwb * s->wpb_backsub;
   MVBA_CUDA(cudaFuncSetAttribute(backsub_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_backsub));
+  {  // pass A: stage as many blocks per round as ~100 KB allows (two CTAs per SM)
+    const size_t budget = std::min<size_t>((size_t)dev_smem, 100 * 1024) - 3 * MVBA_CAM_MAXACT * 4 - 64;
+    int bi = (int)(budget / ((size_t)3 * s->cam_ldj * 8));
+    bi = std::min(256, (bi / 32) * 32);
+    if (bi < 32) return fail(MVBA_EINVAL, "mvba: pass A staging does not fit shared memory");
+    s->cam_batch = bi;
+    s->smem_cam = cam_pass_smem(bi, s->cam_ldj);
+    MVBA_CUDA(cudaFuncSetAttribute(camera_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_cam));
+    int occ_cam = 1;
+    MVBA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_cam, camera_pass_kernel, MVBA_CAM_THREADS, s->smem_cam));
+    s->grid_cam = std::max(1, std::min(s->nchunks, h->sm_count * std::max(occ_cam, 1)));
+  }
   int occ = 1;
   MVBA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, build_kernel, 32 * s->wpb_build, s->smem_build));
   s->grid_build = std::max(1, std::min((v.P + s->wpb_build - 1) / s->wpb_build, h->sm_count * std::max(occ, 1)));

@@ -31,12 +31,22 @@ inline int run_build(mvba_problem* h, const mvba_solve_options& o, double radius
   a.radius = radius; a.min_diag = o.min_lm_diagonal; a.max_diag = o.max_lm_diagonal;
   a.Hinv = s->Hinv.p; a.ge = s->ge.p; a.diagE = s->diagE.p; a.cost = s->red.p + s->o_cost;
   a.mode = mode; a.maxposes = s->maxposes; a.maxdz = s->maxdz; a.vwmax = s->vwmax;
-  if (v.P > 0) {
-    if (s->tm) s->tm->begin(9);
-    build_kernel<<<s->grid_build, 32 * s->wpb_build, s->smem_build, h->stream>>>(v, a, s->R);
-    if (s->tm) s->tm->end();
-    h->launches++; s->build_launches++;
+  a.trk_list = nullptr; a.ntrk = v.P;
+  if (s->tm) s->tm->begin(9);
+  if (s->nchunks > 0 && s->nf > 0) {  // pass A: F'F, F'r, diag(F'F) by camera image
+    CamPassArgs ca{};
+    ca.x = h->d_x.p; ca.tab = h->d_tab.p; ca.dtab = h->d_dtab.p; ca.jscale_f = a.jscale_f;
+    ca.chunk_cam = s->chunk_cam.p; ca.chunk_beg = s->chunk_beg.p; ca.citems = s->citems.p; ca.nchunks = s->nchunks;
+    ca.batch_items = s->cam_batch; ca.ldj = s->cam_ldj; ca.mode = mode;
+    camera_pass_kernel<<<s->grid_cam, MVBA_CAM_THREADS, s->smem_cam, h->stream>>>(v, ca, s->R);
+    h->launches++;
   }
+  if (v.P > 0) {  // pass B: landmark blocks, Schur elimination
+    build_kernel<<<s->grid_build, 32 * s->wpb_build, s->smem_build, h->stream>>>(v, a, s->R);
+    h->launches++;
+  }
+  if (s->tm) s->tm->end();
+  s->build_launches++;
   MVBA_CUDA(cudaGetLastError());
   return allreduce(h, s->red.p, s->red_n, 8, 0);
 }

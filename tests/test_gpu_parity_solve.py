@@ -1,0 +1,73 @@
+"""GPU parity, part 2: the device Levenberg-Marquardt solve (mvba_solve) against the CPU oracle's
+Ceres-1.14-style LM on the same seeded pass.
+
+Tolerances (BASELINE.json north_star): converged cost 1e-6 relative, optimised poses 1e-6 m /
+1e-6 rad (quaternion components are compared at 1e-6 as well), landmarks 1e-6 m.  The oracle runs
+with exact (forward-mode dual) Jacobians here so that both sides follow the same trajectory; the
+Ceres-rule numeric-diff variant is exercised in test_oracle_golden.py."""
+import numpy as np
+import pytest
+
+from multiview_b200 import _abi, synth
+
+pytestmark = pytest.mark.gpu
+
+CASES = {
+    "pinhole": dict(sensors="pinhole", num_ref=16, num_landmarks=600, obs_per_track=4, float_rig=False),
+    "rig3": dict(sensors="rig3", num_ref=16, num_landmarks=800, obs_per_track=5, outlier_frac=0.02),
+    "rig3_ragged_intr": dict(sensors="rig3b", num_ref=12, num_landmarks=600, obs_per_track=6, ragged=True,
+                             float_intrinsics=("focal_length", "optical_center", "distortion"), intr_noise=1e-3),
+    "depth_mesh": dict(sensors="rig3", num_ref=12, num_landmarks=500, obs_per_track=5, depth=True, mesh=True,
+                       depth_tri_weight=1000.0, depth_mesh_weight=50.0, mesh_tri_weight=25.0, tri_weight=0.5,
+                       float_d2i=True, float_scale=True),
+    "rpc": dict(sensors="rpc", num_ref=12, num_landmarks=500, obs_per_track=6, float_rig=False,
+                float_intrinsics=("focal_length", "distortion"), intr_noise=1e-3),
+    "no_rig": dict(sensors="rig3", num_ref=10, num_landmarks=400, obs_per_track=5, no_rig=True),
+    "offsets": dict(sensors="rig3", num_ref=12, num_landmarks=500, obs_per_track=5, float_offsets=True),
+}
+
+
+ITERS = {"depth_mesh": 5}
+
+
+def _run(lib, prefix, pr, snap, iters, **kw):
+    pr.restore(snap)
+    b = _abi.Binding(lib, prefix, pr)
+    s, log = b.solve(_abi.default_options(max_num_iterations=iters), **kw)
+    out = pr.snapshot()
+    b.close()
+    return s, log, out
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_lm_trajectory_and_converged_state(name, oracle_lib, product_lib):
+    pr = synth.make_problem(seed=23, **CASES[name])
+    snap = pr.snapshot()
+    # depth_mesh floats depth_to_image + scale + rig at once: the gauge is only weakly held, so round-off
+    # differences grow along it after a few iterations; it is compared while both are on the same path.
+    iters = ITERS.get(name, 12)
+    so, lo, xo = _run(oracle_lib, "oracle_", pr, snap, iters, jac_mode=1)
+    sg, lg, xg = _run(product_lib, "mvba_", pr, snap, iters)
+    assert sg.num_kernel_launches > 0
+    assert abs(sg.initial_cost - so.initial_cost) <= 1e-9 * so.initial_cost
+    assert sg.num_iterations == so.num_iterations
+    # same accept/reject decisions and cost trajectory
+    for a, b in zip(lg, lo):
+        assert a["step_accepted"] == b["step_accepted"]
+        assert abs(a["cost"] - b["cost"]) <= 1e-6 * b["cost"]
+    assert abs(sg.final_cost - so.final_cost) <= 1e-6 * so.final_cost
+    for k in xo:
+        if xo[k].size:
+            assert np.abs(xo[k] - xg[k]).max() <= 1e-6, (k, np.abs(xo[k] - xg[k]).max())
+
+
+def test_solve_is_repeatable(product_lib):
+    """Atomics make the summation order free; two runs must still agree far below the parity bar."""
+    pr = synth.make_problem(seed=5, **CASES["rig3"])
+    snap = pr.snapshot()
+    s1, _, x1 = _run(product_lib, "mvba_", pr, snap, 8)
+    s2, _, x2 = _run(product_lib, "mvba_", pr, snap, 8)
+    assert abs(s1.final_cost - s2.final_cost) <= 1e-10 * s1.final_cost
+    for k in x1:
+        if x1[k].size:
+            assert np.abs(x1[k] - x2[k]).max() <= 1e-8
