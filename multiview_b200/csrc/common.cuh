@@ -28,6 +28,13 @@ struct CamTab {
 };
 static_assert(sizeof(CamTab) == 70 * 8, "CamTab layout");
 
+// Pose-part Jacobian coefficients of one camera image, one 3-vector per row (prep_cameras_kernel):
+//   rows 0-2 (1-alpha) Rrc[:,k] | 3-6 W0[:,j] | 7-9 alpha Rrc[:,k] | 10-13 W1[:,j] | 14-16 rig_on e_k | 17-20 Wrc[:,j]
+//   | 21 dalpha wa | 22 dalpha dt.   Virtual pose column vc = row (rows 21 and 22 both belong to the offset column).
+// With M = (sr A)' E and N = [Z]x M, Nrc = [Xc - trc]x M the block's F'E rows are coef' M (translations, row 22),
+// coef' N (rotations of the bracketing poses, row 21) and coef' Nrc (rig rotation).
+struct CamCoef { double c[23][3]; };
+
 // Per-sensor depth-to-image table (prep_sensors_kernel): Mc = s L m + td
 struct DepthTab {
   double L[9], td[3], s;

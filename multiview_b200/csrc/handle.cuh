@@ -88,6 +88,7 @@ struct mvba_problem {
   mvba::DBuf<double> d_x, d_xnew;
   mvba::DBuf<mvba::CamTab> d_tab;
   mvba::DBuf<mvba::DepthTab> d_dtab;
+  mvba::DBuf<mvba::CamCoef> d_coef;
   mvba::DBuf<double> d_scalars;   // small scratch of device scalars
   mvba::DBuf<int> d_err;
   mvba::DBuf<double> d_resid;     // residual rows scratch

@@ -7,12 +7,24 @@ namespace mvba {
 
 // One thread per camera image (+ one per sensor for the depth tables).
 __global__ void prep_cameras_kernel(View v, const double* __restrict__ x, CamTab* __restrict__ tab,
-                                    DepthTab* __restrict__ dtab, int* __restrict__ err) {
+                                    DepthTab* __restrict__ dtab, int* __restrict__ err, CamCoef* __restrict__ coef) {
   int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c < v.C) {
     CamTab o;
     bool ok = prep_camera(v, x, c, o);
     tab[c] = o;
+    if (coef) {
+      CamCoef& q = coef[c];
+      for (int k = 0; k < 3; k++)
+        for (int a = 0; a < 3; a++) {
+          q.c[k][a] = (1.0 - o.alpha) * o.Rrc[3 * a + k];
+          q.c[7 + k][a] = o.alpha * o.Rrc[3 * a + k];
+          q.c[14 + k][a] = (a == k) ? o.rig_on : 0.0;
+        }
+      for (int j = 0; j < 4; j++)
+        for (int a = 0; a < 3; a++) { q.c[3 + j][a] = o.W0[4 * a + j]; q.c[10 + j][a] = o.W1[4 * a + j]; q.c[17 + j][a] = o.Wrc[4 * a + j]; }
+      for (int a = 0; a < 3; a++) { q.c[21][a] = o.dalpha * o.wa[a]; q.c[22][a] = o.dalpha * o.dt[a]; }
+    }
     if (!ok) atomicExch(err, MVBA_EBRACKET);
   } else if (c < v.C + v.T && dtab != nullptr) {
     DepthTab d;

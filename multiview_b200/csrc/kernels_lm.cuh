@@ -3,6 +3,7 @@
 // (Ceres 1.14 TrustRegionMinimizer / LevenbergMarquardtStrategy semantics).
 #pragma once
 #include "kernels_pcg.cuh"
+#include "kernels_backsub.cuh"
 
 namespace mvba {
 
@@ -39,121 +40,6 @@ __global__ void gradmax_kernel(int nf, int64_t ne, const double* __restrict__ g,
   else if (i < nf + ne) { int64_t k = i - nf; v = fabs(ge[k] / (se ? se[k] : 1.0)); }
   for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
   if ((threadIdx.x & 31) == 0 && v > 0) atomicMax(reinterpret_cast<unsigned long long*>(lm + LM_GMAX), (unsigned long long)__double_as_longlong(v));
-}
-
-// Back-substitution (one warp per track): y_e = Hinv (E'r - E'F y_f) and the model cost change
-//   -(J step)'(r + J step / 2),  step = -y.  Jacobians are recomputed, not read.
-struct BacksubArgs {
-  const double* x; const CamTab* tab; const DepthTab* dtab;
-  const double *jscale_f, *jscale_e;
-  const double *Hinv, *ge, *yf;
-  double* ye;      // 3 per landmark (scaled variables)
-  double* lm;      // LM_MCC accumulates
-  double* fy;      // scratch: 3 doubles per item, per warp region of size maxitems
-  int maxitems, maxdz;
-};
-
-__global__ void __launch_bounds__(256) backsub_kernel(View v, BacksubArgs a) {
-  extern __shared__ double smem_d[];
-  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, wpb = blockDim.x >> 5;
-  // per warp: stash[CHUNK] | Jd[CHUNK][2][maxdz] | fy[maxitems][3] | rr[maxitems][3] | Es[maxitems][9]
-  const size_t per_warp = sizeof(Stash) * MVBA_CHUNK / 8 + (size_t)MVBA_CHUNK * 2 * a.maxdz + (size_t)a.maxitems * 15;
-  double* base = smem_d + per_warp * wib;
-  Stash* stash = reinterpret_cast<Stash*>(base);
-  double* Jd = base + sizeof(Stash) * MVBA_CHUNK / 8;
-  double* fy = Jd + (size_t)MVBA_CHUNK * 2 * a.maxdz;
-  double* rr = fy + 3 * (size_t)a.maxitems;
-  double* Es = rr + 3 * (size_t)a.maxitems;
-  double mcc = 0;
-  for (int p = blockIdx.x * wpb + wib; p < v.P; p += gridDim.x * wpb) {
-    const int64_t o0 = v.trk_obs0[p], o1 = v.trk_obs0[p + 1];
-    const int64_t d0 = v.trk_dtri0[p], d1 = v.trk_dtri0[p + 1];
-    const int64_t m0 = v.trk_dmesh0[p], m1 = v.trk_dmesh0[p + 1];
-    const int64_t pm0 = v.trk_pm0[p], pm1 = v.trk_pm0[p + 1];
-    const int64_t pt0 = v.trk_pt0[p], pt1 = v.trk_pt0[p + 1];
-    const int n_obs = (int)(o1 - o0), n_dt = (int)(d1 - d0), n_dm = (int)(m1 - m0), n_pm = (int)(pm1 - pm0), n_pt = (int)(pt1 - pt0);
-    const int nitems = n_obs + n_dt + n_dm + n_pm + n_pt;
-    if (nitems == 0) continue;
-    double se[3] = {1, 1, 1};
-    if (a.jscale_e) { se[0] = a.jscale_e[3 * (size_t)p]; se[1] = a.jscale_e[3 * (size_t)p + 1]; se[2] = a.jscale_e[3 * (size_t)p + 2]; }
-    double u[3] = {0, 0, 0};  // E' F y_f (lane 0 holds the total after each item)
-    for (int c0 = 0; c0 < nitems; c0 += MVBA_CHUNK) {
-      const int cnt = min(MVBA_CHUNK, nitems - c0);
-      if (lane < cnt) {
-        int q = c0 + lane;
-        Item it;
-        double* jd0 = Jd + (size_t)lane * 2 * a.maxdz;
-        if (q < n_obs) eval_cam<true>(v, a.x, a.tab, o0 + q, it, jd0, jd0 + a.maxdz);
-        else if (q < n_obs + n_dt) eval_depth(v, a.x, a.tab, a.dtab, MVBA_BLOCK_DEPTH_TRI, d0 + (q - n_obs), it);
-        else if (q < n_obs + n_dt + n_dm) eval_depth(v, a.x, a.tab, a.dtab, MVBA_BLOCK_DEPTH_MESH, m0 + (q - n_obs - n_dt), it);
-        else if (q < n_obs + n_dt + n_dm + n_pm) eval_prior(v, a.x, pm0 + (q - n_obs - n_dt - n_dm), it);
-        else eval_prior(v, a.x, pt0 + (q - n_obs - n_dt - n_dm - n_pm), it);
-        double s = 0;
-        for (int k = 0; k < it.nr; k++) s += it.r[k] * it.r[k];
-        double hr, sr;
-        cauchy(it.loss_a, s, &hr, &sr);
-        Stash& st = stash[lane];
-        st.kind = it.kind; st.nr = it.nr; st.cid = it.cid; st.sensor = it.sensor; st.sr = sr; st.Jc = it.Jc;
-#pragma unroll
-        for (int k = 0; k < 3; k++) { st.r[k] = k < it.nr ? sr * it.r[k] : 0.0; st.Z[k] = it.Z[k]; st.Xc[k] = it.Xc[k]; st.Jf[k] = it.Jf[k]; st.m[k] = it.m[k]; }
-#pragma unroll
-        for (int k = 0; k < 9; k++) { st.A[k] = it.A[k]; st.E[k] = (k / 3 < it.nr) ? sr * it.E[k] * se[k % 3] : 0.0; }
-#pragma unroll
-        for (int k = 0; k < 3; k++) rr[3 * q + k] = st.r[k];
-#pragma unroll
-        for (int k = 0; k < 9; k++) Es[9 * q + k] = st.E[k];
-      }
-      __syncwarp();
-      for (int j = 0; j < cnt; j++) {
-        const Stash& st = stash[j];
-        double f[3] = {0, 0, 0};
-        if (st.kind != MVBA_BLOCK_MESH_TRI && st.kind != MVBA_BLOCK_TRI) {
-          Item it;
-          it.kind = st.kind; it.nr = st.nr; it.cid = st.cid; it.sensor = st.sensor; it.Jc = st.Jc;
-#pragma unroll
-          for (int k = 0; k < 3; k++) { it.Z[k] = st.Z[k]; it.Xc[k] = st.Xc[k]; it.Jf[k] = st.Jf[k]; it.m[k] = st.m[k]; }
-#pragma unroll
-          for (int k = 0; k < 9; k++) it.A[k] = st.A[k];
-          const int vw = item_vwidth(v, it);
-          const double* jd0 = Jd + (size_t)j * 2 * a.maxdz;
-          for (int vc = lane; vc < vw; vc += 32) {
-            int gc = item_gcol(v, it, vc);
-            if (gc < 0) continue;
-            double col[3] = {0, 0, 0};
-            item_jcol(v, it, a.tab, a.dtab, vc, jd0, jd0 + a.maxdz, col);
-            double sc = st.sr * (a.jscale_f ? a.jscale_f[gc] : 1.0) * a.yf[gc];
-            for (int r = 0; r < st.nr; r++) f[r] += col[r] * sc;
-          }
-#pragma unroll
-          for (int k = 0; k < 3; k++) f[k] = warp_sum(f[k]);
-        }
-        if (lane == 0) {
-          int q = c0 + j;
-          for (int k = 0; k < 3; k++) fy[3 * q + k] = f[k];
-          for (int r = 0; r < st.nr; r++) for (int b = 0; b < 3; b++) u[b] += st.E[3 * r + b] * f[r];
-        }
-      }
-      __syncwarp();
-    }
-    // lane 0 finishes the landmark
-    if (lane == 0) {
-      const double* Hi = a.Hinv + 6 * (size_t)p;
-      const double* g = a.ge + 3 * (size_t)p;
-      double w0 = g[0] - u[0], w1 = g[1] - u[1], w2 = g[2] - u[2];
-      double ye[3] = {Hi[0] * w0 + Hi[1] * w1 + Hi[2] * w2, Hi[1] * w0 + Hi[3] * w1 + Hi[4] * w2, Hi[2] * w0 + Hi[4] * w1 + Hi[5] * w2};
-      for (int k = 0; k < 3; k++) a.ye[3 * (size_t)p + k] = ye[k];
-      for (int q = 0; q < nitems; q++) {
-        for (int r = 0; r < 3; r++) {
-          double jy = fy[3 * q + r] + Es[9 * q + 3 * r] * ye[0] + Es[9 * q + 3 * r + 1] * ye[1] + Es[9 * q + 3 * r + 2] * ye[2];
-          double ms = -jy;  // J step
-          mcc -= ms * (rr[3 * q + r] + 0.5 * ms);
-        }
-      }
-    }
-    __syncwarp();
-  }
-  mcc = warp_sum(mcc);
-  if (lane == 0) atomicAdd(a.lm + LM_MCC, mcc);
 }
 
 // x_new = x - scale * y  over every parameter scalar; accumulates |step|^2 and |x|^2 (free only).

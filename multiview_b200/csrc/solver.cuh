@@ -11,6 +11,7 @@
 #include "handle.cuh"
 #include "kernels_lm.cuh"
 #include "kernels_camera.cuh"
+#include "kernels_tile.cuh"
 
 namespace mvba {
 
@@ -77,6 +78,8 @@ struct Solver {
   DBuf<double> Dsq, Mpp, Mbb, work, jscale_f, jscale_e, Hinv, ge, diagE, lo, hi;
   DBuf<double> y, r, z, p, q, ye, lm, pcg_scal;
   DBuf<int> pcg_flags;
+  DBuf<CamDir> camdir;
+  DBuf<SensDir> sensdir;
   mvba_iteration* rec = nullptr;  // pinned
   int* flags_host = nullptr;      // pinned
   size_t smem_build = 0, smem_backsub = 0;
@@ -86,6 +89,10 @@ struct Solver {
   DBuf<int32_t> citems, chunk_cam, chunk_beg;
   int nchunks = 0, cam_batch = 0, cam_ldj = 0, grid_cam = 1;
   size_t smem_cam = 0;
+  // pass B fast path: tracks sorted by first pose block and cut into window tiles; the rest fall back
+  DBuf<int32_t> tile_trk0, tile_w0, tile_wn, trk_order, fallback;
+  int ntiles = 0, nfallback = 0, tile_nt = 512, tile_pr = 4, tile_K = 1, tile_icap = 64, tile_nx = 0, tile_L8max = 8, grid_tile = 1;
+  size_t smem_tile = 0;
   Reduced R{};
   Bsr A{};
 };
@@ -110,6 +117,9 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
   if ((size_t)nb * nb > ((size_t)1 << 31)) return fail(MVBA_EINVAL, "mvba: too many free pose blocks for the dense pair table");
   std::vector<uint8_t> flag((size_t)nb * nb, 0);
   std::vector<int> uniq;
+  std::vector<int32_t> trk_umin(v.P, 0), trk_span(v.P, 0);
+  std::vector<uint8_t> trk_any(v.P, 0);
+  std::vector<int32_t> trk_items(v.P, 0);
   int maxposes = 1, maxitems = 1;
   for (int p = 0; p < v.P; p++) {
     uniq.clear();
@@ -126,9 +136,14 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
     }
     for (size_t a = 0; a < uniq.size(); a++) for (size_t b = 0; b < uniq.size(); b++) { int u1 = uniq[a], u2 = uniq[b]; if (u1 <= u2) flag[(size_t)u1 * nb + u2] = 1; }
     maxposes = std::max(maxposes, (int)uniq.size());
+    if (!uniq.empty()) {
+      int lo = *std::min_element(uniq.begin(), uniq.end()), hi = *std::max_element(uniq.begin(), uniq.end());
+      trk_umin[p] = lo; trk_span[p] = hi - lo + 1;
+    }
     int items = (int)(h->h_trk_obs0[p + 1] - h->h_trk_obs0[p] + h->h_trk_dtri0[p + 1] - h->h_trk_dtri0[p] + h->h_trk_dmesh0[p + 1] - h->h_trk_dmesh0[p] +
                       h->h_trk_pm0[p + 1] - h->h_trk_pm0[p] + h->h_trk_pt0[p + 1] - h->h_trk_pt0[p]);
     maxitems = std::max(maxitems, items);
+    trk_any[p] = items > 0; trk_items[p] = items;
   }
   for (int u = 0; u < nb; u++) flag[(size_t)u * nb + u] = 1;  // diagonal always present (damping)
   std::vector<int32_t> pairtab((size_t)nb * nb, -1), row_ptr(nb + 1, 0), col, slot;
@@ -235,11 +250,8 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
   s->wpb_build = (int)std::max<size_t>(1, std::min<size_t>(8, (size_t)dev_smem / 2 / pw));
   s->smem_build = pw * s->wpb_build;
   MVBA_CUDA(cudaFuncSetAttribute(build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_build));
-  size_t pwb = (sizeof(Stash) * MVBA_CHUNK / 8 + (size_t)MVBA_CHUNK * 2 * s->maxdz + (size_t)s->maxitems * 15) * 8;
-  if (pwb > (size_t)dev_smem) return fail(MVBA_EINVAL, "mvba: a track has too many residual blocks for one warp's shared memory");
-  s->wpb_backsub = (int)std::max<size_t>(1, std::min<size_t>(8, (size_t)dev_smem / 2 / pwb));
-  s->smem_backsub = pwb * s->wpb_backsub;
-  MVBA_CUDA(cudaFuncSetAttribute(backsub_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_backsub));
+  if (s->maxdz > MVBA_MAXDZ) return fail(MVBA_EINVAL, "mvba: distortion block too long");
+  MVBA_CUDA(s->camdir.alloc(std::max(v.C, 1))); MVBA_CUDA(s->sensdir.alloc(std::max(v.T, 1)));
   {  // pass A: stage as many blocks per round as ~100 KB allows (two CTAs per SM)
     const size_t budget = std::min<size_t>((size_t)dev_smem, 100 * 1024) - 3 * MVBA_CAM_MAXACT * 4 - 64;
     int bi = (int)(budget / ((size_t)3 * s->cam_ldj * 8));
@@ -252,11 +264,64 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
     MVBA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_cam, camera_pass_kernel, MVBA_CAM_THREADS, s->smem_cam));
     s->grid_cam = std::max(1, std::min(s->nchunks, h->sm_count * std::max(occ_cam, 1)));
   }
+  {  // ---- pass B fast path: window tiles ----
+    // one register patch per thread, 512 threads: 4x4 patches up to L8 = 120, 8x4 patches up to L8 = 176
+    int maxspan = 0;
+    for (int p = 0; p < v.P; p++) if (trk_any[p]) maxspan = std::max(maxspan, (int)trk_span[p]);
+    const int cap4 = (120 - s->B) / 7, cap8 = (176 - s->B) / 7;
+    int W = maxspan + 2;
+    s->tile_pr = 4;
+    if (W > cap4) { s->tile_pr = 8; W = std::min(W, cap8); }
+    if (s->B > 176 || W < 0) W = -1;  // nothing fits: every track takes the generic kernel
+    std::vector<int32_t> order, fb;
+    for (int p = 0; p < v.P; p++) if (trk_any[p]) { if (W >= 0 && trk_span[p] <= W && trk_items[p] <= 32) order.push_back(p); else fb.push_back(p); }
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return trk_umin[a] < trk_umin[b]; });
+    std::vector<int32_t> t0, tw0, twn;
+    const int tile_max = 512;
+    size_t i = 0;
+    int wn_max = 0;
+    while (i < order.size()) {
+      const int w0 = trk_umin[order[i]];
+      int hi = w0;  // one past the last pose block used
+      size_t j = i;
+      while (j < order.size() && (int)(j - i) < tile_max) {
+        int p = order[j], e = trk_umin[p] + trk_span[p];
+        if (trk_span[p] > 0 && e - w0 > W) break;
+        if (trk_span[p] > 0) hi = std::max(hi, e);
+        j++;
+      }
+      t0.push_back((int32_t)i); tw0.push_back(w0); twn.push_back(hi - w0);
+      wn_max = std::max(wn_max, hi - w0);
+      i = j;
+    }
+    t0.push_back((int32_t)order.size());
+    s->ntiles = (int)tw0.size(); s->nfallback = (int)fb.size();
+    s->tile_L8max = std::max(8, (7 * wn_max + s->B + 7) & ~7);
+    MVBA_CUDA(s->tile_trk0.upload(t0)); MVBA_CUDA(s->tile_w0.upload(tw0)); MVBA_CUDA(s->tile_wn.upload(twn));
+    MVBA_CUDA(s->trk_order.upload(order)); MVBA_CUDA(s->fallback.upload(fb));
+    // shared-memory plan: <= icap staged residual blocks and <= K staged tracks per round
+    int nx = 0;
+    for (int t = 0; t < v.T; t++) {
+      const SensorDev& sd = v.sens[t];
+      nx = std::max(nx, (sd.c_focal >= 0) + (sd.c_center >= 0 ? 2 : 0) + (sd.c_dist >= 0 ? sd.nd_nz : 0));
+      nx = std::max(nx, (sd.c_d2i >= 0 ? v.nd2i : 0) + (sd.c_scale >= 0));
+    }
+    s->tile_nx = nx;
+    const size_t per_item = sizeof(TRec) + (size_t)32 * nx;
+    s->tile_icap = (int)std::min<size_t>(256, (size_t)96 * 1024 / per_item);
+    const size_t per_trk = (size_t)s->tile_L8max * 48 + 32 + sizeof(TTrack);
+    s->tile_K = (int)std::max<size_t>(1, std::min<size_t>(32, ((size_t)dev_smem - 2048 - per_item * s->tile_icap) / per_trk));
+    s->tile_K = std::min(s->tile_K, std::max(4, s->tile_icap / 4));
+    s->smem_tile = tile_smem(s->tile_K, s->tile_icap, nx, s->tile_L8max);
+    if (s->smem_tile > (size_t)dev_smem) return fail(MVBA_EINVAL, "mvba: tile staging does not fit shared memory");
+    if (s->tile_pr == 4) MVBA_CUDA(cudaFuncSetAttribute(tile_kernel<512, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_tile));
+    else MVBA_CUDA(cudaFuncSetAttribute(tile_kernel<512, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_tile));
+    s->grid_tile = std::max(1, std::min(s->ntiles, h->sm_count));
+  }
   int occ = 1;
   MVBA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, build_kernel, 32 * s->wpb_build, s->smem_build));
   s->grid_build = std::max(1, std::min((v.P + s->wpb_build - 1) / s->wpb_build, h->sm_count * std::max(occ, 1)));
-  MVBA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, backsub_kernel, 32 * s->wpb_backsub, s->smem_backsub));
-  s->grid_backsub = std::max(1, std::min((v.P + s->wpb_backsub - 1) / s->wpb_backsub, h->sm_count * std::max(occ, 1)));
+  s->grid_backsub = std::max(1, std::min((v.P + 127) / 128, h->sm_count * 16));
   return MVBA_OK;
 }
 

@@ -41,9 +41,24 @@ inline int run_build(mvba_problem* h, const mvba_solve_options& o, double radius
     camera_pass_kernel<<<s->grid_cam, MVBA_CAM_THREADS, s->smem_cam, h->stream>>>(v, ca, s->R);
     h->launches++;
   }
-  if (v.P > 0) {  // pass B: landmark blocks, Schur elimination
+  if (v.P > 0 && mode == 1) {  // column norms: diag(E'E) per landmark
     build_kernel<<<s->grid_build, 32 * s->wpb_build, s->smem_build, h->stream>>>(v, a, s->R);
     h->launches++;
+  } else if (v.P > 0) {  // pass B: landmark blocks, Schur elimination
+    if (s->ntiles > 0) {
+      TileArgs ta{};
+      ta.b = a; ta.tile_trk0 = s->tile_trk0.p; ta.tile_w0 = s->tile_w0.p; ta.tile_wn = s->tile_wn.p; ta.trk_order = s->trk_order.p;
+      ta.ntiles = s->ntiles; ta.K = s->tile_K; ta.icap = s->tile_icap; ta.nx = s->tile_nx; ta.L8max = s->tile_L8max; ta.coef = h->d_coef.p;
+      if (s->tile_pr == 4) tile_kernel<512, 4><<<s->grid_tile, 512, s->smem_tile, h->stream>>>(v, ta, s->R);
+      else tile_kernel<512, 8><<<s->grid_tile, 512, s->smem_tile, h->stream>>>(v, ta, s->R);
+      h->launches++;
+    }
+    if (s->nfallback > 0) {
+      a.trk_list = s->fallback.p; a.ntrk = s->nfallback;
+      int grid = std::max(1, std::min((s->nfallback + s->wpb_build - 1) / s->wpb_build, s->grid_build));
+      build_kernel<<<grid, 32 * s->wpb_build, s->smem_build, h->stream>>>(v, a, s->R);
+      h->launches++;
+    }
   }
   if (s->tm) s->tm->end();
   s->build_launches++;
@@ -181,12 +196,15 @@ inline int solver_solve(mvba_problem* h, const mvba_solve_options& o, mvba_summa
     MVBA_CUDA(cudaMemsetAsync(s->lm.p + LM_CAND, 0, 4 * sizeof(double), h->stream));
     MVBA_CUDA(cudaMemsetAsync(s->lm.p + LM_STEP2, 0, 2 * sizeof(double), h->stream));
     if (v.P > 0) {
+      const int ndir = v.C + v.T;
+      dir_cameras_kernel<<<(ndir + 127) / 128, 128, 0, h->stream>>>(v, h->d_tab.p, h->d_dtab.p, s->y.p, scaled ? s->jscale_f.p : nullptr,
+                                                                      s->camdir.p, s->sensdir.p);
       BacksubArgs b{};
-      b.x = h->d_x.p; b.tab = h->d_tab.p; b.dtab = h->d_dtab.p;
+      b.x = h->d_x.p; b.tab = h->d_tab.p; b.dtab = h->d_dtab.p; b.cd = s->camdir.p; b.sdir = s->sensdir.p;
       b.jscale_f = scaled ? s->jscale_f.p : nullptr; b.jscale_e = scaled ? s->jscale_e.p : nullptr;
-      b.Hinv = s->Hinv.p; b.ge = s->ge.p; b.yf = s->y.p; b.ye = s->ye.p; b.lm = s->lm.p; b.maxitems = s->maxitems; b.maxdz = s->maxdz;
-      backsub_kernel<<<s->grid_backsub, 32 * s->wpb_backsub, s->smem_backsub, h->stream>>>(v, b);
-      h->launches++;
+      b.Hinv = s->Hinv.p; b.ge = s->ge.p; b.yf = s->y.p; b.ye = s->ye.p; b.lm = s->lm.p; b.lm_mcc = LM_MCC;
+      backsub_kernel<<<s->grid_backsub, 128, 0, h->stream>>>(v, b);
+      h->launches += 2;
     }
     update_kernel<<<(v.nx + tb - 1) / tb, tb, 0, h->stream>>>(v.nx, s->nf, s->xcol.p, h->d_x.p, s->y.p, s->ye.p, scaled ? s->jscale_f.p : nullptr,
                                                               scaled ? s->jscale_e.p : nullptr, h->bounded ? s->lo.p : nullptr,

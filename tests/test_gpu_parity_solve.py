@@ -27,7 +27,9 @@ CASES = {
 }
 
 
-ITERS = {"depth_mesh": 5}
+# Cases whose later iterations have rejected steps with 40-70 CG iterations: the Q-based CG stopping test then flips
+# on round-off, after which the two runs are on different (equally valid) paths.  They are compared on the common path.
+ITERS = {"depth_mesh": 5, "rig3_ragged_intr": 4}
 
 
 def _run(lib, prefix, pr, snap, iters, **kw):
@@ -58,7 +60,24 @@ def test_lm_trajectory_and_converged_state(name, oracle_lib, product_lib):
     assert abs(sg.final_cost - so.final_cost) <= 1e-6 * so.final_cost
     for k in xo:
         if xo[k].size:
-            assert np.abs(xo[k] - xg[k]).max() <= 1e-6, (k, np.abs(xo[k] - xg[k]).max())
+            err = _param_error(k, xo[k], xg[k], pr)
+            assert err <= 1e-6, (k, err)
+
+
+def _param_error(name, a, b, pr):
+    """Largest difference in metres / radians / native units.  Pose blocks are tx ty tz qx qy qz qw with
+    the quaternion a free 4-vector that the functors normalise (dense_map_utils.cc:171-178): its LENGTH
+    is pure gauge, so rotations are compared as the angle between the normalised quaternions."""
+    rigid = name in ("world_to_ref", "ref_to_cam", "world_to_cam") or (name == "depth_to_image" and not pr.affine_depth)
+    if not rigid:
+        return float(np.abs(a - b).max())
+    A, B = a.reshape(-1, 7), b.reshape(-1, 7)
+    qa = A[:, 3:] / np.linalg.norm(A[:, 3:], axis=1, keepdims=True)
+    qb = B[:, 3:] / np.linalg.norm(B[:, 3:], axis=1, keepdims=True)
+    dot = np.clip(np.abs(np.sum(qa * qb, axis=1)), 0.0, 1.0)
+    sin_half = np.sqrt(np.maximum(0.0, 1.0 - dot * dot))   # accurate for tiny angles, unlike arccos(dot)
+    ang = 2.0 * np.arcsin(np.minimum(1.0, sin_half))
+    return float(max(np.abs(A[:, :3] - B[:, :3]).max(), ang.max()))
 
 
 def test_solve_is_repeatable(product_lib):
@@ -70,4 +89,4 @@ def test_solve_is_repeatable(product_lib):
     assert abs(s1.final_cost - s2.final_cost) <= 1e-10 * s1.final_cost
     for k in x1:
         if x1[k].size:
-            assert np.abs(x1[k] - x2[k]).max() <= 1e-8
+            assert _param_error(k, x1[k], x2[k], pr) <= 1e-8
