@@ -850,6 +850,7 @@ int oracle_time_linearize(void* h, int32_t jac_mode, int32_t num_threads, double
   return 0;
 }
 int oracle_max_threads(void) { return omp_get_max_threads(); }
+void oracle_cauchy(double a, double s, double* rho, double* sqrt_rho1) { oracle::cauchy(a, s, rho, sqrt_rho1); }
 // array <-> transform helpers exported for the host-logic tests.
 void oracle_array_to_rigid(const double* a, double* m12) { auto A = oracle::array_to_rigid<double>(a); for (int i = 0; i < 3; i++) { for (int j = 0; j < 3; j++) m12[4 * i + j] = A.m[i][j]; m12[4 * i + 3] = A.t[i]; } }
 void oracle_rigid_to_array(const double* m12, double* a) { oracle::Aff<double> A; for (int i = 0; i < 3; i++) { for (int j = 0; j < 3; j++) A.m[i][j] = m12[4 * i + j]; A.t[i] = m12[4 * i + 3]; } oracle::rigid_to_array(A, a); }
