@@ -74,9 +74,11 @@ def _param_error(name, a, b, pr):
     A, B = a.reshape(-1, 7), b.reshape(-1, 7)
     qa = A[:, 3:] / np.linalg.norm(A[:, 3:], axis=1, keepdims=True)
     qb = B[:, 3:] / np.linalg.norm(B[:, 3:], axis=1, keepdims=True)
-    dot = np.clip(np.abs(np.sum(qa * qb, axis=1)), 0.0, 1.0)
-    sin_half = np.sqrt(np.maximum(0.0, 1.0 - dot * dot))   # accurate for tiny angles, unlike arccos(dot)
-    ang = 2.0 * np.arcsin(np.minimum(1.0, sin_half))
+    # chord length between the unit quaternions (sign-aligned): |qa - s*qb| = 2 sin(angle/4); accurate to ~1e-16
+    # for tiny angles, unlike arccos(dot) or sqrt(1 - dot^2), whose resolution is sqrt(eps) = 1.5e-8
+    sgn = np.where(np.sum(qa * qb, axis=1) < 0.0, -1.0, 1.0)[:, None]
+    chord = np.linalg.norm(qa - sgn * qb, axis=1)
+    ang = 4.0 * np.arcsin(np.minimum(1.0, 0.5 * chord))
     return float(max(np.abs(A[:, :3] - B[:, :3]).max(), ang.max()))
 
 
