@@ -1,18 +1,22 @@
 // kernels_tile.cuh -- pass B of the normal-equation build, fast path: Schur elimination of a TILE of
 // tracks whose free poses fall inside one window of consecutive pose blocks.
 //
-// The host sorts tracks by their first pose block and cuts the order into tiles (solver.cuh).  Inside a
-// tile every track's local system lives in the same small column space
+// The host sorts tracks by their first pose block and cuts the order into tiles, tiles into ROUNDS of <= K
+// tracks / <= icap residual blocks, and writes STATIC tables for every round (solver.cuh): which residual
+// block each staged slot evaluates, and for every (track, touched parameter block) GROUP the list of staged
+// slots that contribute to it.  Inside a tile every track's local system lives in the same small column space
 //     [ 7 * Wt window pose columns | B border columns ]   (Lt columns, padded to L8 = multiple of 8),
 // so the tile's whole contribution  - sum_tracks (G Hinv) G'  is a dense symmetric Lt x Lt matrix.  It is
 // kept in REGISTERS, spread over the CTA as 4x4 (or 8x4) patches (thread = patch), and goes to the reduced system
-// with one atomicAdd per entry per tile instead of one per entry per track.  Per round of <= K tracks:
+// with one atomicAdd per entry per tile instead of one per entry per track.  Per round:
 //   phase b1  one THREAD per residual block: residual, analytic dr/dXc (A) and dr/dX (E), Cauchy
-//             correction, then the three 3x3 matrices  M = (sr A)'E, N = [Z]x M, Nrc = [Xc - t_rc]x M.
-//             Every pose / rig / offset column of F'E is  coef' {M | N | Nrc}  with a per-image
-//             3-vector coef (CamCoef, common.cuh), so no Jacobian column is formed per observation.
-//   phase b2  one warp per track: E'E, E'r over its blocks, Hinv, G = F'E into shared memory
-//             (dense-in-window rows, zero where the track has no observation), Y = G Hinv
+//             correction, M = (sr A)'E, and the block's share of E'E, E'r.
+//   phase b2  one THREAD per (track, group, row): row of G = F'E as a GATHER over the group's contributors:
+//             every pose / rig / offset row of one block's F'E is  d' M  with  d = coef, coef x Z or
+//             coef x (Xc - t_rc)  for a per-image 3-vector coef (CamCoef, common.cuh), so no Jacobian column is
+//             formed per observation, nothing is accumulated with atomics and no warp waits on another.
+//             Threads k < kc meanwhile sum E'E, E'r of track k and invert.
+//   phase b3  all threads: Y = G Hinv (dense-in-window rows)
 //   phase c   all threads: rank-3K update of the register patches from the staged tracks
 //             (24 LDS per 48 DFMA), plus rhs -= G Hinv E'r
 //   flush     once per tile
@@ -22,13 +26,27 @@
 
 namespace mvba {
 
+// Static round tables (host-built, solver.cuh).  A slot is the position of a residual block in the round's staging
+// buffer; a track's blocks occupy consecutive slots in the order CAM, DEPTH_TRI, DEPTH_MESH, MESH_TRI prior, TRI prior.
+struct TBlk { int32_t idx; int32_t kind; };                       // index inside its kind's array
+struct TTrk { int32_t p; int16_t q0, n; };                        // landmark, first slot, number of slots
+struct TGrp { uint32_t con0; uint16_t lcol; uint8_t k, ncon; };   // contributors, first local column, track slot; ncon bit 7: offset column (1 row)
+static_assert(sizeof(TBlk) == 8 && sizeof(TTrk) == 8 && sizeof(TGrp) == 8, "tile table layout");
+// contributor: (slot << 2) | role, role 0 beg pose (coef rows 0-6), 1 end pose (7-13), 2 rig transform (14-20), 3 offset (21, 22)
+
 struct TileArgs {
   BuildArgs b;
   const CamCoef* coef;
-  const int32_t* tile_trk0;   // ntiles + 1: range into trk_order
   const int32_t* tile_w0;     // first pose block of the window
   const int32_t* tile_wn;     // number of pose blocks in the window
-  const int32_t* trk_order;   // track ids, tile-major
+  const int32_t* tile_round0; // ntiles + 1: range of rounds
+  const int32_t* round_trk0;  // nrounds + 1: range into ttrk
+  const int32_t* round_blk0;  // nrounds + 1: range into blk
+  const int32_t* round_grp0;  // nrounds + 1: range into grp
+  const TBlk* blk;
+  const TTrk* ttrk;
+  const TGrp* grp;
+  const uint16_t* con;
   int ntiles;
   int K;                      // tracks staged per round (<= 32)
   int icap;                   // residual blocks staged per round
@@ -36,35 +54,30 @@ struct TileArgs {
   int L8max;                  // padded local width the shared buffers are sized for
 };
 
-
-// What phase b1 leaves per residual block.  lb / le / lr / lo: LOCAL column of the first beg-pose, end-pose and
-// rig-transform column and of the offset column in the tile's column space (-1: constant or absent).
+// What phase b1 leaves per residual block.
 struct TRec {
-  double M[9], N[9], Nrc[9], H[6], g[3];
-  int cid, lb, le, lr, lo, nx, fcols, pad;  // nx: staged non-pose entries; fcols: 0 for the landmark priors
+  double M[9], Z[3], y[3], H[6], g[3];
+  int cid, nx;  // cid < 0: no f columns (landmark priors); nx: staged non-pose entries
 };
-static_assert(sizeof(TRec) == 320, "TRec layout");
+static_assert(sizeof(TRec) == 200, "TRec layout");
 
-struct TTrack { int p, start[5], count[5], q0; };  // CSR ranges of the five block kinds, first staged slot
-
-// Shared memory: Gs[K][L8max][3] | Ys[K][L8max][3] | ves[K][4] | Xs[icap][4 nx] | rec[icap] | trk[K+1]
+// Shared memory: Gs[K][L8max][3] | Ys[K][L8max][3] | ves[K][4] | His[K][6] | cs[L8max] | Xs[icap][4 nx] | rec[icap]
 __host__ __device__ inline size_t tile_smem(int K, int icap, int nx, int L8max) {
-  return ((size_t)K * L8max * 6 + (size_t)K * 4 + (size_t)icap * 4 * nx) * 8 + (size_t)icap * sizeof(TRec) + (size_t)(K + 1) * sizeof(TTrack) + 16;
+  return ((size_t)K * L8max * 6 + (size_t)K * 10 + (size_t)L8max + (size_t)icap * 4 * nx) * 8 + (size_t)icap * sizeof(TRec) + 16;
 }
 
-// Phase b1: one thread evaluates residual block `j` of staged track `tk`.  Nothing here is Jacobi-scaled on
-// the f side (tile_fold scales whole columns once); E carries the landmark scaling.
-__device__ inline double tile_eval(const View& v, const BuildArgs& a, const Reduced& S, const TTrack& tk, int j, int w0, int Wt,
+// Phase b1: one thread evaluates one residual block.  Nothing here is Jacobi-scaled on the f side (phase b2 scales
+// whole columns once); E carries the landmark scaling.
+__device__ inline double tile_eval(const View& v, const BuildArgs& a, const Reduced& S, const TBlk bk, int Wt,
                                    TRec& rec, double* X, double* jd) {
   Item it;
-  const int p = tk.p;
-  int kind = 0;
-  while (j >= tk.count[kind]) { j -= tk.count[kind]; kind++; }
-  const int64_t idx = (int64_t)tk.start[kind] + j;
+  const int kind = bk.kind;
+  const int64_t idx = bk.idx;
   if (kind == 0) eval_cam<true>(v, a.x, a.tab, idx, it, jd, jd + MVBA_MAXDZ);
   else if (kind == 1) eval_depth(v, a.x, a.tab, a.dtab, MVBA_BLOCK_DEPTH_TRI, idx, it);
   else if (kind == 2) eval_depth(v, a.x, a.tab, a.dtab, MVBA_BLOCK_DEPTH_MESH, idx, it);
   else eval_prior(v, a.x, idx, it);
+  const int p = it.pid;
   double s = 0;
   for (int k = 0; k < it.nr; k++) s += it.r[k] * it.r[k];
   double hr, sr;
@@ -86,34 +99,22 @@ __device__ inline double tile_eval(const View& v, const BuildArgs& a, const Redu
   for (int k = 0; k < 6; k++) rec.H[k] = H[k];
 #pragma unroll
   for (int k = 0; k < 3; k++) rec.g[k] = g[k];
-  rec.cid = it.cid; rec.lb = -1; rec.le = -1; rec.lr = -1; rec.lo = -1; rec.nx = 0; rec.fcols = 0;
+  rec.cid = -1; rec.nx = 0;
   if (kind >= 3) return hr;  // priors: no f columns
-  rec.fcols = 1;
+  rec.cid = it.cid;
   const SensorDev& sd = v.sens[it.sensor];
-  {
-    const int p0 = v.cam_p0[it.cid], p1 = v.cam_p1[it.cid];
-    const int cb = v.pose_col[p0], ce = p1 >= 0 ? v.pose_col[p1] : -1;
-    rec.lb = cb < 0 ? -1 : cb - 7 * w0;
-    rec.le = ce < 0 ? -1 : ce - 7 * w0;
-    rec.lr = sd.c_rig < 0 ? -1 : 7 * Wt + (sd.c_rig - S.npc);
-    rec.lo = sd.c_off < 0 ? -1 : 7 * Wt + (sd.c_off - S.npc);
-  }
-  // M[a][b] = sum_r sr A[r][a] Es[r][b];  N = [Z]x M;  Nrc = [Xc - t_rc]x M
+  // M[a][b] = sum_r sr A[r][a] Es[r][b];  the rotation rows use  coef'[Z]x M = (coef x Z)' M,  so Z and y = Xc - t_rc are kept
   const double* trc = a.tab[it.cid].trc;
-  const double y[3] = {it.Xc[0] - __ldg(trc), it.Xc[1] - __ldg(trc + 1), it.Xc[2] - __ldg(trc + 2)};
 #pragma unroll
-  for (int b = 0; b < 3; b++) {
-    double m[3];
+  for (int k = 0; k < 3; k++) { rec.Z[k] = it.Z[k]; rec.y[k] = it.Xc[k] - __ldg(trc + k); }
+#pragma unroll
+  for (int b = 0; b < 3; b++)
 #pragma unroll
     for (int aa = 0; aa < 3; aa++) {
       double t = 0;
       for (int r = 0; r < it.nr; r++) t += it.A[3 * r + aa] * Es[3 * r + b];
-      m[aa] = sr * t;
+      rec.M[3 * aa + b] = sr * t;
     }
-    rec.M[b] = m[0]; rec.M[3 + b] = m[1]; rec.M[6 + b] = m[2];
-    rec.N[b] = it.Z[1] * m[2] - it.Z[2] * m[1]; rec.N[3 + b] = it.Z[2] * m[0] - it.Z[0] * m[2]; rec.N[6 + b] = it.Z[0] * m[1] - it.Z[1] * m[0];
-    rec.Nrc[b] = y[1] * m[2] - y[2] * m[1]; rec.Nrc[3 + b] = y[2] * m[0] - y[0] * m[2]; rec.Nrc[6 + b] = y[0] * m[1] - y[1] * m[0];
-  }
   // free non-pose columns (focal, centre, distortion | depth transform, scale): direct J'E with the target column
   if (sd.c_focal >= 0 || sd.c_center >= 0 || sd.c_dist >= 0 || sd.c_d2i >= 0 || sd.c_scale >= 0) {
     const int vw = item_vwidth(v, it);
@@ -137,96 +138,39 @@ __device__ inline double tile_eval(const View& v, const BuildArgs& a, const Redu
   return hr;
 }
 
-// Phase b2: one warp folds the staged blocks of one track into G (dense-in-window rows), Hinv, Y.
-// Lane = coefficient row of CamCoef (23 rows); blocks are walked four at a time so that the
-// coefficient loads (L2) of a group are in flight together.
-__device__ inline void tile_fold(const TileArgs& ta, const Reduced& S, const TTrack& tk, const TRec* rec, const double* Xs,
-                                 int w0, int Wt, int Lt, int L8, double* G, double* Y, double* ve_out, int lane) {
-  const BuildArgs& a = ta.b;
-  const int p = tk.p;
-  const int n = tk.count[0] + tk.count[1] + tk.count[2] + tk.count[3] + tk.count[4];
-  for (int li = lane; li < 3 * L8; li += 32) G[li] = 0;
-  double H[6] = {0, 0, 0, 0, 0, 0}, gE[3] = {0, 0, 0};
-  for (int i = lane; i < n; i += 32) {
-    const TRec& r = rec[tk.q0 + i];
-#pragma unroll
-    for (int k = 0; k < 6; k++) H[k] += r.H[k];
-#pragma unroll
-    for (int k = 0; k < 3; k++) gE[k] += r.g[k];
-  }
-#pragma unroll
-  for (int k = 0; k < 6; k++) H[k] = warp_sum(H[k]);
-#pragma unroll
-  for (int k = 0; k < 3; k++) gE[k] = warp_sum(gE[k]);
-  __syncwarp();
-  const int row = lane;
-  const int msel = (row >= 17 && row <= 20) ? 2 : ((row >= 3 && row <= 6) || (row >= 10 && row <= 13) || row == 21) ? 1 : 0;
-  const int role = row < 7 ? 0 : row < 14 ? 1 : row < 21 ? 2 : 3;
-  const int roff = row < 7 ? row : row < 14 ? row - 7 : row < 21 ? row - 14 : 0;
-  for (int i0 = 0; i0 < n; i0 += 4) {
-    int li[4];
-    double c[4][3];
-#pragma unroll
-    for (int u = 0; u < 4; u++) {
-      li[u] = -1;
-      if (i0 + u < n && row < 23) {
-        const TRec& r = rec[tk.q0 + i0 + u];
-        const int base = role == 0 ? r.lb : role == 1 ? r.le : role == 2 ? r.lr : r.lo;
-        if (r.fcols && base >= 0) {
-          li[u] = base + roff;
-          const double* cf = ta.coef[r.cid].c[row];
-          c[u][0] = __ldg(cf); c[u][1] = __ldg(cf + 1); c[u][2] = __ldg(cf + 2);
-        }
+// Phase b2: row `row` of group `gr` of G = F'E for one staged track, gathered over the group's contributors and
+// Jacobi-scaled.  G points at the track's dense-in-window rows.
+__device__ __forceinline__ void tile_gather(const TileArgs& ta, const TGrp gr, int row, const TRec* __restrict__ rec,
+                                            const double* __restrict__ cs, double* __restrict__ G) {
+  const bool single = (gr.ncon & 0x80) != 0;
+  const int ncon = gr.ncon & 0x7f;
+  if (row >= (single ? 1 : 7)) return;
+  double o0 = 0, o1 = 0, o2 = 0;
+  for (int c = 0; c < ncon; c++) {
+    const unsigned cb = __ldg(ta.con + gr.con0 + c);
+    const TRec& r = rec[cb >> 2];
+    const int role = cb & 3;
+    double d0, d1, d2;
+    if (role < 3) {
+      const double* cf = ta.coef[r.cid].c[7 * role + row];
+      const double c0 = __ldg(cf), c1 = __ldg(cf + 1), c2 = __ldg(cf + 2);
+      if (row < 3) { d0 = c0; d1 = c1; d2 = c2; }  // translations: coef' M
+      else {                                        // rotations: coef' [w]x M = (coef x w)' M, w = Z or Xc - t_rc
+        const double* w = role == 2 ? r.y : r.Z;
+        d0 = c1 * w[2] - c2 * w[1]; d1 = c2 * w[0] - c0 * w[2]; d2 = c0 * w[1] - c1 * w[0];
       }
+    } else {  // time offset: dalpha (wa x Z + dt)
+      const double* cf = ta.coef[r.cid].c[21];
+      const double c0 = __ldg(cf), c1 = __ldg(cf + 1), c2 = __ldg(cf + 2);
+      d0 = c1 * r.Z[2] - c2 * r.Z[1] + __ldg(cf + 3); d1 = c2 * r.Z[0] - c0 * r.Z[2] + __ldg(cf + 4); d2 = c0 * r.Z[1] - c1 * r.Z[0] + __ldg(cf + 5);
     }
-#pragma unroll
-    for (int u = 0; u < 4; u++) {
-      if (i0 + u >= n) break;
-      const TRec& r = rec[tk.q0 + i0 + u];
-      double out[3] = {0, 0, 0};
-      if (li[u] >= 0) {
-        const double* m = msel == 0 ? r.M : msel == 1 ? r.N : r.Nrc;
-#pragma unroll
-        for (int b = 0; b < 3; b++) out[b] = c[u][0] * m[b] + c[u][1] * m[3 + b] + c[u][2] * m[6 + b];
-      }
-      // the offset column has two rows (21: wa' N, 22: dt' M)
-      if (r.lo >= 0) {
-#pragma unroll
-        for (int b = 0; b < 3; b++) { const double o22 = __shfl_sync(0xffffffffu, out[b], 22); if (row == 21) out[b] += o22; }
-      }
-      if (row < 22 && li[u] >= 0) { G[3 * li[u]] += out[0]; G[3 * li[u] + 1] += out[1]; G[3 * li[u] + 2] += out[2]; }
-      if (r.nx > 0) {  // non-pose columns staged by phase b1 (distinct columns, disjoint from the pose part)
-        const double* X = Xs + (size_t)(tk.q0 + i0 + u) * 4 * ta.nx;
-        for (int k = lane; k < r.nx; k += 32) {
-          const int l2 = (int)X[4 * k + 3];
-          G[3 * l2] += X[4 * k]; G[3 * l2 + 1] += X[4 * k + 1]; G[3 * l2 + 2] += X[4 * k + 2];
-        }
-      }
-      __syncwarp();
-    }
+    o0 = fma(d0, r.M[0], fma(d1, r.M[3], fma(d2, r.M[6], o0)));
+    o1 = fma(d0, r.M[1], fma(d1, r.M[4], fma(d2, r.M[7], o1)));
+    o2 = fma(d0, r.M[2], fma(d1, r.M[5], fma(d2, r.M[8], o2)));
   }
-  H[0] += fmin(fmax(H[0], a.min_diag), a.max_diag) / a.radius;
-  H[3] += fmin(fmax(H[3], a.min_diag), a.max_diag) / a.radius;
-  H[5] += fmin(fmax(H[5], a.min_diag), a.max_diag) / a.radius;
-  double Hi[6];
-  inv_sym3(H, Hi);
-  if (lane < 6) a.Hinv[6 * (size_t)p + lane] = Hi[lane];
-  if (lane < 3) a.ge[3 * (size_t)p + lane] = gE[lane];
-  if (lane == 0) {
-    ve_out[0] = Hi[0] * gE[0] + Hi[1] * gE[1] + Hi[2] * gE[2];
-    ve_out[1] = Hi[1] * gE[0] + Hi[3] * gE[1] + Hi[4] * gE[2];
-    ve_out[2] = Hi[2] * gE[0] + Hi[4] * gE[1] + Hi[5] * gE[2];
-  }
-  // Jacobi column scaling once per local column, then Y = G Hinv
-  for (int l = lane; l < L8; l += 32) {
-    double sc = 1.0;
-    if (a.jscale_f && l < Lt) sc = a.jscale_f[l < 7 * Wt ? 7 * w0 + l : S.npc + (l - 7 * Wt)];
-    const double g0 = G[3 * l] * sc, g1 = G[3 * l + 1] * sc, g2 = G[3 * l + 2] * sc;
-    G[3 * l] = g0; G[3 * l + 1] = g1; G[3 * l + 2] = g2;
-    Y[3 * l] = Hi[0] * g0 + Hi[1] * g1 + Hi[2] * g2;
-    Y[3 * l + 1] = Hi[1] * g0 + Hi[3] * g1 + Hi[4] * g2;
-    Y[3 * l + 2] = Hi[2] * g0 + Hi[4] * g1 + Hi[5] * g2;
-  }
+  const int l = gr.lcol + row;
+  const double sc = cs[l];
+  G[3 * l] = o0 * sc; G[3 * l + 1] = o1 * sc; G[3 * l + 2] = o2 * sc;
 }
 
 // NT threads; register patches of PR x 4 (PR = 4 or 8), one per thread, on or above the diagonal.
@@ -239,16 +183,16 @@ __global__ void __launch_bounds__(NT, 1) tile_kernel(View v, TileArgs a, Reduced
   double* Gs = smem_d;
   double* Ys = Gs + (size_t)K * a.L8max * 3;
   double* ves = Ys + (size_t)K * a.L8max * 3;
-  double* Xs = ves + (size_t)K * 4;
+  double* His = ves + (size_t)K * 4;
+  double* cs = His + (size_t)K * 6;
+  double* Xs = cs + a.L8max;
   TRec* rec = reinterpret_cast<TRec*>(Xs + (size_t)a.icap * 4 * a.nx);
-  TTrack* trk = reinterpret_cast<TTrack*>(rec + a.icap);
-  __shared__ int s_kc, s_nit;
   const int B = S.B;
+  const size_t gstride = (size_t)a.L8max * 3;
   double cost_acc = 0;
   double jd[2 * MVBA_MAXDZ];
 
   for (int t = blockIdx.x; t < a.ntiles; t += gridDim.x) {
-    const int t0 = a.tile_trk0[t], t1 = a.tile_trk0[t + 1];
     const int w0 = a.tile_w0[t], Wt = a.tile_wn[t];
     const int Lt = 7 * Wt + B, L8 = (Lt + 7) & ~7;
     const int nb4 = L8 >> 2, nbr = L8 / PR;
@@ -266,46 +210,80 @@ __global__ void __launch_bounds__(NT, 1) tile_kernel(View v, TileArgs a, Reduced
 #pragma unroll
       for (int j = 0; j < 4; j++) acc[i][j] = 0;
     double rhs_acc = 0;
+    // Jacobi scale of every local column (the previous tile's readers are behind its last barrier)
+    for (int l = tid; l < a.L8max; l += NT)
+      cs[l] = (a.b.jscale_f && l < Lt) ? a.b.jscale_f[l < 7 * Wt ? 7 * w0 + l : S.npc + (l - 7 * Wt)] : 1.0;
 
-    int r0 = t0;
-    while (r0 < t1) {
-      // ---- round set-up: as many tracks as fit K slots and icap residual blocks (warp 0) ----
-      if (wib == 0) {
-        int cnt = 0;
-        TTrack tk{};
-        if (lane < K && r0 + lane < t1) {
-          const int p = a.trk_order[r0 + lane];
-          tk.p = p;
-          tk.start[0] = (int)v.trk_obs0[p]; tk.count[0] = (int)(v.trk_obs0[p + 1] - v.trk_obs0[p]);
-          tk.start[1] = (int)v.trk_dtri0[p]; tk.count[1] = (int)(v.trk_dtri0[p + 1] - v.trk_dtri0[p]);
-          tk.start[2] = (int)v.trk_dmesh0[p]; tk.count[2] = (int)(v.trk_dmesh0[p + 1] - v.trk_dmesh0[p]);
-          tk.start[3] = (int)v.trk_pm0[p]; tk.count[3] = (int)(v.trk_pm0[p + 1] - v.trk_pm0[p]);
-          tk.start[4] = (int)v.trk_pt0[p]; tk.count[4] = (int)(v.trk_pt0[p + 1] - v.trk_pt0[p]);
-          cnt = tk.count[0] + tk.count[1] + tk.count[2] + tk.count[3] + tk.count[4];
-        }
-        int incl = cnt;
+    const int rd0 = a.tile_round0[t], rd1 = a.tile_round0[t + 1];
+    for (int rd = rd0; rd < rd1; rd++) {
+      const int trk0 = a.round_trk0[rd], kc = a.round_trk0[rd + 1] - trk0;
+      const int blk0 = a.round_blk0[rd], nit = a.round_blk0[rd + 1] - blk0;
+      const int grp0 = a.round_grp0[rd], ngrp = a.round_grp0[rd + 1] - grp0;
+      // ---- phase b1: one thread per residual block; everyone clears G ----
+      for (int q = tid; q < nit; q += NT)
+        cost_acc += tile_eval(v, a.b, S, a.blk[blk0 + q], Wt, rec[q], Xs + (size_t)q * 4 * a.nx, jd);
+      {
+        double2* gz = reinterpret_cast<double2*>(Gs);
+        const int nz = (int)((size_t)kc * gstride / 2);
+        for (int i = tid; i < nz; i += NT) gz[i] = make_double2(0.0, 0.0);
+      }
+      __syncthreads();
+      // ---- phase b2: one thread per (group, row) gathers a row of G; threads k < kc reduce and invert E'E ----
+      for (int i = tid; i < 8 * ngrp; i += NT) {
+        const TGrp gr = a.grp[grp0 + (i >> 3)];
+        tile_gather(a, gr, i & 7, rec, cs, Gs + (size_t)gr.k * gstride);
+      }
+      if (tid < kc) {
+        const TTrk tk = a.ttrk[trk0 + tid];
+        double H[6] = {0, 0, 0, 0, 0, 0}, gE[3] = {0, 0, 0};
+        for (int i = 0; i < tk.n; i++) {
+          const TRec& r = rec[tk.q0 + i];
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) { int u = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += u; }
-        const bool fits = cnt > 0 && incl <= a.icap;
-        const unsigned mk = __ballot_sync(0xffffffffu, fits);
-        const int kc = mk == 0xffffffffu ? 32 : __ffs(~mk) - 1;  // in order: the first track that does not fit ends the round
-        tk.q0 = incl - cnt;
-        if (lane < kc) trk[lane] = tk;
-        if (lane == kc - 1) s_nit = incl;
-        if (lane == 0) s_kc = kc;
+          for (int k = 0; k < 6; k++) H[k] += r.H[k];
+#pragma unroll
+          for (int k = 0; k < 3; k++) gE[k] += r.g[k];
+        }
+        H[0] += fmin(fmax(H[0], a.b.min_diag), a.b.max_diag) / a.b.radius;
+        H[3] += fmin(fmax(H[3], a.b.min_diag), a.b.max_diag) / a.b.radius;
+        H[5] += fmin(fmax(H[5], a.b.min_diag), a.b.max_diag) / a.b.radius;
+        double Hi[6];
+        inv_sym3(H, Hi);
+#pragma unroll
+        for (int k = 0; k < 6; k++) { a.b.Hinv[6 * (size_t)tk.p + k] = Hi[k]; His[6 * tid + k] = Hi[k]; }
+#pragma unroll
+        for (int k = 0; k < 3; k++) a.b.ge[3 * (size_t)tk.p + k] = gE[k];
+        ves[4 * tid] = Hi[0] * gE[0] + Hi[1] * gE[1] + Hi[2] * gE[2];
+        ves[4 * tid + 1] = Hi[1] * gE[0] + Hi[3] * gE[1] + Hi[4] * gE[2];
+        ves[4 * tid + 2] = Hi[2] * gE[0] + Hi[4] * gE[1] + Hi[5] * gE[2];
+      }
+      if (a.nx > 0) {  // free intrinsics / depth columns staged by phase b1: a warp per track, disjoint from the gathered columns
+        for (int k = wib; k < kc; k += NW) {
+          const TTrk tk = a.ttrk[trk0 + k];
+          double* G = Gs + (size_t)k * gstride;
+          for (int i = 0; i < tk.n; i++) {
+            const int nxi = rec[tk.q0 + i].nx;
+            const double* X = Xs + (size_t)(tk.q0 + i) * 4 * a.nx;
+            for (int kk = lane; kk < nxi; kk += 32) {
+              const int l2 = (int)X[4 * kk + 3];
+              const double sc = cs[l2];
+              G[3 * l2] += X[4 * kk] * sc; G[3 * l2 + 1] += X[4 * kk + 1] * sc; G[3 * l2 + 2] += X[4 * kk + 2] * sc;
+            }
+            __syncwarp();
+          }
+        }
       }
       __syncthreads();
-      const int kc = s_kc, nit = s_nit;
-      // ---- phase b1: one thread per residual block ----
-      for (int q = tid; q < nit; q += NT) {
-        int k = 0;
-        while (k + 1 < kc && trk[k + 1].q0 <= q) k++;
-        cost_acc += tile_eval(v, a.b, S, trk[k], q - trk[k].q0, w0, Wt, rec[q], Xs + (size_t)q * 4 * a.nx, jd);
+      // ---- phase b3: Y = G Hinv ----
+      for (int i = tid; i < kc * L8; i += NT) {
+        const int k = i / L8, l = i - k * L8;
+        const double* g = Gs + (size_t)k * gstride + 3 * l;
+        const double* Hi = His + 6 * k;
+        double* y = Ys + (size_t)k * gstride + 3 * l;
+        const double g0 = g[0], g1 = g[1], g2 = g[2];
+        y[0] = Hi[0] * g0 + Hi[1] * g1 + Hi[2] * g2;
+        y[1] = Hi[1] * g0 + Hi[3] * g1 + Hi[4] * g2;
+        y[2] = Hi[2] * g0 + Hi[4] * g1 + Hi[5] * g2;
       }
-      __syncthreads();
-      // ---- phase b2: one warp per track ----
-      for (int k = wib; k < kc; k += NW)
-        tile_fold(a, S, trk[k], rec, Xs, w0, Wt, Lt, L8, Gs + (size_t)k * a.L8max * 3, Ys + (size_t)k * a.L8max * 3, ves + 4 * k, lane);
       __syncthreads();
       // ---- phase c: register patches += Y G' over the staged tracks ----
       if (worker) {
@@ -332,7 +310,6 @@ __global__ void __launch_bounds__(NT, 1) tile_kernel(View v, TileArgs a, Reduced
         }
       }
       __syncthreads();
-      r0 += kc;
     }
     // ---- flush: local column -> reduced column; window poses are consecutive pose blocks ----
     if (worker) {

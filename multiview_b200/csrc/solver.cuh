@@ -90,8 +90,10 @@ struct Solver {
   int nchunks = 0, cam_batch = 0, cam_ldj = 0, grid_cam = 1;
   size_t smem_cam = 0;
   // pass B fast path: tracks sorted by first pose block and cut into window tiles; the rest fall back
-  DBuf<int32_t> tile_trk0, tile_w0, tile_wn, trk_order, fallback;
-  int ntiles = 0, nfallback = 0, tile_nt = 512, tile_pr = 4, tile_K = 1, tile_icap = 64, tile_nx = 0, tile_L8max = 8, grid_tile = 1;
+  // (static round tables: staged blocks, per-track slots, gather groups and their contributors, kernels_tile.cuh)
+  DBuf<int32_t> tile_w0, tile_wn, tile_round0, round_trk0, round_blk0, round_grp0, fallback;
+  DBuf<TBlk> t_blk; DBuf<TTrk> t_trk; DBuf<TGrp> t_grp; DBuf<uint16_t> t_con;
+  int ntiles = 0, nrounds = 0, nfallback = 0, tile_nt = 512, tile_pr = 4, tile_K = 1, tile_icap = 64, tile_nx = 0, tile_L8max = 8, grid_tile = 1;
   size_t smem_tile = 0;
   Reduced R{};
   Bsr A{};
@@ -297,8 +299,7 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
     t0.push_back((int32_t)order.size());
     s->ntiles = (int)tw0.size(); s->nfallback = (int)fb.size();
     s->tile_L8max = std::max(8, (7 * wn_max + s->B + 7) & ~7);
-    MVBA_CUDA(s->tile_trk0.upload(t0)); MVBA_CUDA(s->tile_w0.upload(tw0)); MVBA_CUDA(s->tile_wn.upload(twn));
-    MVBA_CUDA(s->trk_order.upload(order)); MVBA_CUDA(s->fallback.upload(fb));
+    MVBA_CUDA(s->tile_w0.upload(tw0)); MVBA_CUDA(s->tile_wn.upload(twn)); MVBA_CUDA(s->fallback.upload(fb));
     // shared-memory plan: <= icap staged residual blocks and <= K staged tracks per round
     int nx = 0;
     for (int t = 0; t < v.T; t++) {
@@ -307,15 +308,83 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
       nx = std::max(nx, (sd.c_d2i >= 0 ? v.nd2i : 0) + (sd.c_scale >= 0));
     }
     s->tile_nx = nx;
-    const size_t per_item = sizeof(TRec) + (size_t)32 * nx;
-    s->tile_icap = (int)std::min<size_t>(256, (size_t)96 * 1024 / per_item);
-    const size_t per_trk = (size_t)s->tile_L8max * 48 + 32 + sizeof(TTrack);
-    s->tile_K = (int)std::max<size_t>(1, std::min<size_t>(32, ((size_t)dev_smem - 2048 - per_item * s->tile_icap) / per_trk));
-    s->tile_K = std::min(s->tile_K, std::max(4, s->tile_icap / 4));
+    {
+      const size_t per_item = sizeof(TRec) + (size_t)32 * nx;
+      const size_t per_trk = (size_t)s->tile_L8max * 48 + 80;
+      const size_t avail = (size_t)dev_smem - 2048 - (size_t)s->tile_L8max * 8;
+      // mean residual blocks per track decides how the budget is split between tracks and staged blocks
+      double mean_items = 1.0;
+      { double tot = 0; for (int p : order) tot += trk_items[p]; if (!order.empty()) mean_items = std::max(1.0, tot / order.size()); }
+      int K = (int)std::min<double>(32.0, (double)avail / ((double)per_trk + 1.15 * mean_items * (double)per_item));
+      K = std::max(1, K);
+      size_t icap = (avail - (size_t)K * per_trk) / per_item;
+      icap = std::min<size_t>(icap, 511);
+      if (icap < 32) { K = 1; icap = std::min<size_t>(511, (avail - per_trk) / per_item); }
+      if (icap < 32) return fail(MVBA_EINVAL, "mvba: tile staging does not fit shared memory");
+      s->tile_K = K; s->tile_icap = (int)icap;
+    }
     s->smem_tile = tile_smem(s->tile_K, s->tile_icap, nx, s->tile_L8max);
     if (s->smem_tile > (size_t)dev_smem) return fail(MVBA_EINVAL, "mvba: tile staging does not fit shared memory");
     if (s->tile_pr == 4) MVBA_CUDA(cudaFuncSetAttribute(tile_kernel<512, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_tile));
     else MVBA_CUDA(cudaFuncSetAttribute(tile_kernel<512, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_tile));
+    // ---- static round tables ----
+    std::vector<int32_t> tile_round0{0}, round_trk0{0}, round_blk0{0}, round_grp0{0};
+    std::vector<TBlk> blk; std::vector<TTrk> ttrk; std::vector<TGrp> grp; std::vector<uint16_t> con;
+    blk.reserve((size_t)(v.N + v.n_dtri + v.n_dmesh + v.n_prior)); ttrk.reserve(order.size());
+    struct Key { int lcol; int single; std::vector<uint16_t> c; };
+    std::vector<Key> keys;
+    for (int t = 0; t < s->ntiles; t++) {
+      const int w0 = tw0[t], Wt = twn[t];
+      int ti = t0[t];
+      while (ti < t0[t + 1]) {
+        int kc = 0, nit = 0;
+        while (ti + kc < t0[t + 1] && kc < s->tile_K && nit + trk_items[order[ti + kc]] <= s->tile_icap) { nit += trk_items[order[ti + kc]]; kc++; }
+        if (kc == 0) return fail(MVBA_EINVAL, "mvba: a tile track does not fit the staging buffer");
+        int q = 0;
+        for (int k = 0; k < kc; k++) {
+          const int p = order[ti + k];
+          ttrk.push_back(TTrk{p, (int16_t)q, (int16_t)trk_items[p]});
+          keys.clear();
+          auto contribute = [&](int lcol, int single, int slot, int role) {
+            size_t i = 0;
+            while (i < keys.size() && keys[i].lcol != lcol) i++;
+            if (i == keys.size()) keys.push_back(Key{lcol, single, {}});
+            keys[i].c.push_back((uint16_t)((slot << 2) | role));
+          };
+          auto f_block = [&](int64_t obs, int slot) {
+            const int c = h->ocid[obs];
+            const SensorDev& sd = v.sens[h->cam_sensor[c]];
+            const int p0 = h->h_cam_p0[c], p1 = h->h_cam_p1[c];
+            const int cb = h->h_pose_col[p0], ce = p1 >= 0 ? h->h_pose_col[p1] : -1;
+            if (cb >= 0) contribute(cb - 7 * w0, 0, slot, 0);
+            if (ce >= 0) contribute(ce - 7 * w0, 0, slot, 1);
+            if (sd.c_rig >= 0) contribute(7 * Wt + (sd.c_rig - s->npc), 0, slot, 2);
+            if (sd.c_off >= 0) contribute(7 * Wt + (sd.c_off - s->npc), 1, slot, 3);
+          };
+          for (int64_t i = h->h_trk_obs0[p]; i < h->h_trk_obs0[p + 1]; i++) { blk.push_back(TBlk{(int32_t)i, 0}); f_block(i, q++); }
+          for (int64_t j = h->h_trk_dtri0[p]; j < h->h_trk_dtri0[p + 1]; j++) { blk.push_back(TBlk{(int32_t)j, 1}); f_block(h->h_dtri_obs[j], q++); }
+          for (int64_t j = h->h_trk_dmesh0[p]; j < h->h_trk_dmesh0[p + 1]; j++) { blk.push_back(TBlk{(int32_t)j, 2}); f_block(h->h_dmesh_obs[j], q++); }
+          for (int64_t j = h->h_trk_pm0[p]; j < h->h_trk_pm0[p + 1]; j++) { blk.push_back(TBlk{(int32_t)j, 3}); q++; }
+          for (int64_t j = h->h_trk_pt0[p]; j < h->h_trk_pt0[p + 1]; j++) { blk.push_back(TBlk{(int32_t)j, 4}); q++; }
+          for (const Key& key : keys) {
+            if (con.size() >= ((size_t)1 << 32) - 64) return fail(MVBA_EINVAL, "mvba: gather table too large");
+            grp.push_back(TGrp{(uint32_t)con.size(), (uint16_t)key.lcol, (uint8_t)k, (uint8_t)(key.c.size() | (key.single ? 0x80 : 0))});
+            con.insert(con.end(), key.c.begin(), key.c.end());
+          }
+        }
+        ti += kc;
+        round_trk0.push_back((int32_t)ttrk.size()); round_blk0.push_back((int32_t)blk.size()); round_grp0.push_back((int32_t)grp.size());
+      }
+      tile_round0.push_back((int32_t)round_trk0.size() - 1);
+    }
+    s->nrounds = (int)round_trk0.size() - 1;
+    if (con.empty()) con.push_back(0);
+    if (grp.empty()) grp.push_back(TGrp{0, 0, 0, 0});
+    if (blk.empty()) blk.push_back(TBlk{0, 0});
+    if (ttrk.empty()) ttrk.push_back(TTrk{0, 0, 0});
+    MVBA_CUDA(s->tile_round0.upload(tile_round0)); MVBA_CUDA(s->round_trk0.upload(round_trk0)); MVBA_CUDA(s->round_blk0.upload(round_blk0));
+    MVBA_CUDA(s->round_grp0.upload(round_grp0)); MVBA_CUDA(s->t_blk.upload(blk)); MVBA_CUDA(s->t_trk.upload(ttrk)); MVBA_CUDA(s->t_grp.upload(grp));
+    MVBA_CUDA(s->t_con.upload(con));
     s->grid_tile = std::max(1, std::min(s->ntiles, h->sm_count));
   }
   int occ = 1;
