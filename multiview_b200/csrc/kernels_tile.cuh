@@ -30,8 +30,10 @@ namespace mvba {
 // buffer; a track's blocks occupy consecutive slots in the order CAM, DEPTH_TRI, DEPTH_MESH, MESH_TRI prior, TRI prior.
 struct TBlk { int32_t idx; int32_t kind; };                       // index inside its kind's array
 struct TTrk { int32_t p; int16_t q0, n; };                        // landmark, first slot, number of slots
-struct TGrp { uint32_t con0; uint16_t lcol; uint8_t k, ncon; };   // contributors, first local column, track slot; ncon bit 7: offset column (1 row)
-static_assert(sizeof(TBlk) == 8 && sizeof(TTrk) == 8 && sizeof(TGrp) == 8, "tile table layout");
+// gather group: first local column, track slot, contributor count (bit 7: offset column, 1 row), the first four
+// contributors inline, the rest at con[over0 ...]
+struct alignas(16) TGrp { uint32_t over0; uint16_t lcol; uint8_t k, ncon; uint16_t c[4]; };
+static_assert(sizeof(TBlk) == 8 && sizeof(TTrk) == 8 && sizeof(TGrp) == 16, "tile table layout");
 // contributor: (slot << 2) | role, role 0 beg pose (coef rows 0-6), 1 end pose (7-13), 2 rig transform (14-20), 3 offset (21, 22)
 
 struct TileArgs {
@@ -61,9 +63,16 @@ struct TRec {
 };
 static_assert(sizeof(TRec) == 200, "TRec layout");
 
-// Shared memory: Gs[K][L8max][3] | Ys[K][L8max][3] | ves[K][4] | His[K][6] | cs[L8max] | Xs[icap][4 nx] | rec[icap]
+// Row length of the K-major staging matrices: 3 K rounded up so that KK = 4 (mod 16) doubles, which makes the
+// DMMA fragment loads (8 rows x 4 consecutive doubles per half warp) bank-conflict free.
+__host__ __device__ inline int tile_kk(int K) { int kk = 3 * K; while ((kk & 15) != 4) kk++; return kk; }
+
+// Shared memory: Gt[L8max][KK] | Yt[L8max][KK] | ves[KK] | His[K][6] | cs[L8max] | Xs[icap][4 nx] | rec[icap]
+// Gt[l][3 k + b] = row l of G = F'E of staged track k (dense in the window, zero where the track has no block),
+// Yt = G Hinv in the same layout: phase c is the GEMM  C += Yt Gt'  with the staged tracks as the K dimension.
 __host__ __device__ inline size_t tile_smem(int K, int icap, int nx, int L8max) {
-  return ((size_t)K * L8max * 6 + (size_t)K * 10 + (size_t)L8max + (size_t)icap * 4 * nx) * 8 + (size_t)icap * sizeof(TRec) + 16;
+  const size_t KK = tile_kk(K);
+  return (2 * (size_t)L8max * KK + KK + (size_t)K * 6 + (size_t)L8max + (size_t)icap * 4 * nx) * 8 + (size_t)icap * sizeof(TRec) + 16;
 }
 
 // Phase b1: one thread evaluates one residual block.  Nothing here is Jacobi-scaled on the f side (phase b2 scales
@@ -138,77 +147,115 @@ __device__ inline double tile_eval(const View& v, const BuildArgs& a, const Redu
   return hr;
 }
 
+// One contributor's term of a gathered row: d' M with d = coef (translations), coef x Z (pose rotations),
+// coef x (Xc - t_rc) (rig rotation) or dalpha (wa x Z + dt) (time offset; e = second coefficient row).
+__device__ __forceinline__ void gather_term(const TRec& r, int role, int row, const double* c, const double* e, double* o) {
+  double d0, d1, d2;
+  if (role < 3 && row < 3) { d0 = c[0]; d1 = c[1]; d2 = c[2]; }
+  else {
+    const double* w = role == 2 ? r.y : r.Z;
+    d0 = c[1] * w[2] - c[2] * w[1]; d1 = c[2] * w[0] - c[0] * w[2]; d2 = c[0] * w[1] - c[1] * w[0];
+    if (role == 3) { d0 += e[0]; d1 += e[1]; d2 += e[2]; }
+  }
+  o[0] = fma(d0, r.M[0], fma(d1, r.M[3], fma(d2, r.M[6], o[0])));
+  o[1] = fma(d0, r.M[1], fma(d1, r.M[4], fma(d2, r.M[7], o[1])));
+  o[2] = fma(d0, r.M[2], fma(d1, r.M[5], fma(d2, r.M[8], o[2])));
+}
+
 // Phase b2: row `row` of group `gr` of G = F'E for one staged track, gathered over the group's contributors and
-// Jacobi-scaled.  G points at the track's dense-in-window rows.
+// Jacobi-scaled.  G points at the track's three columns of Gt (row stride KK).  The coefficient loads (L2) of the four inline
+// contributors are issued together.
 __device__ __forceinline__ void tile_gather(const TileArgs& ta, const TGrp gr, int row, const TRec* __restrict__ rec,
-                                            const double* __restrict__ cs, double* __restrict__ G) {
+                                            const double* __restrict__ cs, double* __restrict__ G, int KK) {
   const bool single = (gr.ncon & 0x80) != 0;
   const int ncon = gr.ncon & 0x7f;
   if (row >= (single ? 1 : 7)) return;
-  double o0 = 0, o1 = 0, o2 = 0;
-  for (int c = 0; c < ncon; c++) {
-    const unsigned cb = __ldg(ta.con + gr.con0 + c);
-    const TRec& r = rec[cb >> 2];
-    const int role = cb & 3;
-    double d0, d1, d2;
-    if (role < 3) {
-      const double* cf = ta.coef[r.cid].c[7 * role + row];
-      const double c0 = __ldg(cf), c1 = __ldg(cf + 1), c2 = __ldg(cf + 2);
-      if (row < 3) { d0 = c0; d1 = c1; d2 = c2; }  // translations: coef' M
-      else {                                        // rotations: coef' [w]x M = (coef x w)' M, w = Z or Xc - t_rc
-        const double* w = role == 2 ? r.y : r.Z;
-        d0 = c1 * w[2] - c2 * w[1]; d1 = c2 * w[0] - c0 * w[2]; d2 = c0 * w[1] - c1 * w[0];
+  double o[3] = {0, 0, 0};
+  int c = 0;
+  if (!single) {
+    double cf[4][3];
+    int role[4];
+    const TRec* rp[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      const unsigned cb = gr.c[u];
+      rp[u] = rec + (cb >> 2); role[u] = cb & 3;
+      if (u < ncon) {
+        const double* p = ta.coef[rp[u]->cid].c[7 * role[u] + row];
+        cf[u][0] = __ldg(p); cf[u][1] = __ldg(p + 1); cf[u][2] = __ldg(p + 2);
       }
-    } else {  // time offset: dalpha (wa x Z + dt)
-      const double* cf = ta.coef[r.cid].c[21];
-      const double c0 = __ldg(cf), c1 = __ldg(cf + 1), c2 = __ldg(cf + 2);
-      d0 = c1 * r.Z[2] - c2 * r.Z[1] + __ldg(cf + 3); d1 = c2 * r.Z[0] - c0 * r.Z[2] + __ldg(cf + 4); d2 = c0 * r.Z[1] - c1 * r.Z[0] + __ldg(cf + 5);
     }
-    o0 = fma(d0, r.M[0], fma(d1, r.M[3], fma(d2, r.M[6], o0)));
-    o1 = fma(d0, r.M[1], fma(d1, r.M[4], fma(d2, r.M[7], o1)));
-    o2 = fma(d0, r.M[2], fma(d1, r.M[5], fma(d2, r.M[8], o2)));
+#pragma unroll
+    for (int u = 0; u < 4; u++)
+      if (u < ncon) gather_term(*rp[u], role[u], row, cf[u], cf[u], o);
+    c = 4;
+  }
+  for (; c < ncon; c++) {
+    const unsigned cb = c < 4 ? gr.c[c] : __ldg(ta.con + gr.over0 + (c - 4));
+    const TRec& r = rec[cb >> 2];
+    const int rl = cb & 3;
+    const double* p = ta.coef[r.cid].c[rl == 3 ? 21 : 7 * rl + row];
+    const double c3[3] = {__ldg(p), __ldg(p + 1), __ldg(p + 2)};
+    double e3[3] = {0, 0, 0};
+    if (rl == 3) { e3[0] = __ldg(p + 3); e3[1] = __ldg(p + 4); e3[2] = __ldg(p + 5); }
+    gather_term(r, rl, row, c3, e3, o);
   }
   const int l = gr.lcol + row;
   const double sc = cs[l];
-  G[3 * l] = o0 * sc; G[3 * l + 1] = o1 * sc; G[3 * l + 2] = o2 * sc;
+  double* g = G + (size_t)l * KK;
+  g[0] = o[0] * sc; g[1] = o[1] * sc; g[2] = o[2] * sc;
 }
 
-// NT threads; register patches of PR x 4 (PR = 4 or 8), one per thread, on or above the diagonal.
-template <int NT, int PR>
+// D(8x8) += A(8x4) B(4x8) on the FP64 tensor cores: a = A[lane/4][lane%4], b = B[lane%4][lane/4],
+// c0, c1 = C[lane/4][2 (lane%4) + {0, 1}].
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+
+#ifdef MVBA_TILE_PROFILE
+__device__ unsigned long long g_tile_prof[8];
+#define TPROF(slot) do { if (tid == 0) { long long now_ = clock64(); prof_[slot] += now_ - tp_; tp_ = now_; } } while (0)
+#else
+#define TPROF(slot) do { } while (0)
+#endif
+
+// NT threads, one CTA per SM.  Phase c keeps the tile's upper-triangular 8x8 blocks of C in DMMA accumulator
+// fragments: every warp owns up to MAXS consecutive blocks (row-major over the upper block triangle).
+// (MAXS = 4, 8 or 16: instantiated per window width so that narrow windows do not pay for 64 accumulator registers.)
+template <int NT, int MAXS>
 __global__ void __launch_bounds__(NT, 1) tile_kernel(View v, TileArgs a, Reduced S) {
   extern __shared__ double smem_d[];
-  constexpr int NW = NT / 32, STEP = PR / 4;
+  constexpr int NW = NT / 32;
   const int tid = threadIdx.x, lane = tid & 31, wib = tid >> 5;
-  const int K = a.K;
-  double* Gs = smem_d;
-  double* Ys = Gs + (size_t)K * a.L8max * 3;
-  double* ves = Ys + (size_t)K * a.L8max * 3;
-  double* His = ves + (size_t)K * 4;
+  const int K = a.K, KK = tile_kk(K);
+  double* Gt = smem_d;
+  double* Yt = Gt + (size_t)a.L8max * KK;
+  double* ves = Yt + (size_t)a.L8max * KK;
+  double* His = ves + KK;
   double* cs = His + (size_t)K * 6;
   double* Xs = cs + a.L8max;
   TRec* rec = reinterpret_cast<TRec*>(Xs + (size_t)a.icap * 4 * a.nx);
   const int B = S.B;
-  const size_t gstride = (size_t)a.L8max * 3;
+  const int gid = lane >> 2, tig = lane & 3;
   double cost_acc = 0;
   double jd[2 * MVBA_MAXDZ];
+#ifdef MVBA_TILE_PROFILE
+  long long prof_[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tp_ = clock64();
+#endif
+  // Yt columns beyond a round's tracks are multiplied by zeros of Gt: they must be finite
+  for (int i = tid; i < a.L8max * KK + KK; i += NT) Yt[i] = 0.0;
 
   for (int t = blockIdx.x; t < a.ntiles; t += gridDim.x) {
     const int w0 = a.tile_w0[t], Wt = a.tile_wn[t];
     const int Lt = 7 * Wt + B, L8 = (Lt + 7) & ~7;
-    const int nb4 = L8 >> 2, nbr = L8 / PR;
-    const int npatch = nbr * nb4 - STEP * (nbr * (nbr - 1) / 2);  // sum_i (nb4 - STEP i)
-    const bool worker = tid < npatch;
-    int bi = 0, bj = 0;
-    if (worker) {
-      int rem = tid;
-      while (rem >= nb4 - STEP * bi) { rem -= nb4 - STEP * bi; bi++; }
-      bj = STEP * bi + rem;
-    }
-    double acc[PR][4];
+    const int nb8 = L8 >> 3, nblk = nb8 * (nb8 + 1) / 2;
+    const int per = (nblk + NW - 1) / NW;                       // <= MAXS by the host's window cap
+    const int s0 = min(nblk, wib * per), ns = min(nblk, s0 + per) - s0;
+    int bi0 = 0, bj0 = 0;                                       // first block of this warp
+    { int rem = s0; while (bi0 < nb8 && rem >= nb8 - bi0) { rem -= nb8 - bi0; bi0++; } bj0 = bi0 + rem; }
+    double acc[MAXS][2];
 #pragma unroll
-    for (int i = 0; i < PR; i++)
-#pragma unroll
-      for (int j = 0; j < 4; j++) acc[i][j] = 0;
+    for (int i = 0; i < MAXS; i++) { acc[i][0] = 0; acc[i][1] = 0; }
     double rhs_acc = 0;
     // Jacobi scale of every local column (the previous tile's readers are behind its last barrier)
     for (int l = tid; l < a.L8max; l += NT)
@@ -219,19 +266,30 @@ __global__ void __launch_bounds__(NT, 1) tile_kernel(View v, TileArgs a, Reduced
       const int trk0 = a.round_trk0[rd], kc = a.round_trk0[rd + 1] - trk0;
       const int blk0 = a.round_blk0[rd], nit = a.round_blk0[rd + 1] - blk0;
       const int grp0 = a.round_grp0[rd], ngrp = a.round_grp0[rd + 1] - grp0;
-      // ---- phase b1: one thread per residual block; everyone clears G ----
+      // ---- phase b1: one thread per residual block; everyone clears Gt ----
       for (int q = tid; q < nit; q += NT)
         cost_acc += tile_eval(v, a.b, S, a.blk[blk0 + q], Wt, rec[q], Xs + (size_t)q * 4 * a.nx, jd);
       {
-        double2* gz = reinterpret_cast<double2*>(Gs);
-        const int nz = (int)((size_t)kc * gstride / 2);
+        double2* gz = reinterpret_cast<double2*>(Gt);
+        const int nz = L8 * KK / 2;
         for (int i = tid; i < nz; i += NT) gz[i] = make_double2(0.0, 0.0);
       }
+      TPROF(0);
       __syncthreads();
+      TPROF(1);
       // ---- phase b2: one thread per (group, row) gathers a row of G; threads k < kc reduce and invert E'E ----
-      for (int i = tid; i < 8 * ngrp; i += NT) {
-        const TGrp gr = a.grp[grp0 + (i >> 3)];
-        tile_gather(a, gr, i & 7, rec, cs, Gs + (size_t)gr.k * gstride);
+      {
+        const int4* gtab = reinterpret_cast<const int4*>(a.grp + grp0);
+        int i = tid;
+        int4 raw = i < 8 * ngrp ? __ldg(gtab + (i >> 3)) : make_int4(0, 0, 0, 0);
+        while (i < 8 * ngrp) {
+          const int inext = i + NT;
+          const int4 rawn = inext < 8 * ngrp ? __ldg(gtab + (inext >> 3)) : make_int4(0, 0, 0, 0);
+          TGrp gr;
+          *reinterpret_cast<int4*>(&gr) = raw;
+          tile_gather(a, gr, i & 7, rec, cs, Gt + 3 * gr.k, KK);
+          raw = rawn; i = inext;
+        }
       }
       if (tid < kc) {
         const TTrk tk = a.ttrk[trk0 + tid];
@@ -249,89 +307,111 @@ __global__ void __launch_bounds__(NT, 1) tile_kernel(View v, TileArgs a, Reduced
         double Hi[6];
         inv_sym3(H, Hi);
 #pragma unroll
-        for (int k = 0; k < 6; k++) { a.b.Hinv[6 * (size_t)tk.p + k] = Hi[k]; His[6 * tid + k] = Hi[k]; }
+        for (int k = 0; k < 6; k++) { a.b.Hinv[6 * (size_t)tk.p + k] = Hi[k]; His[k * K + tid] = Hi[k]; }
 #pragma unroll
         for (int k = 0; k < 3; k++) a.b.ge[3 * (size_t)tk.p + k] = gE[k];
-        ves[4 * tid] = Hi[0] * gE[0] + Hi[1] * gE[1] + Hi[2] * gE[2];
-        ves[4 * tid + 1] = Hi[1] * gE[0] + Hi[3] * gE[1] + Hi[4] * gE[2];
-        ves[4 * tid + 2] = Hi[2] * gE[0] + Hi[4] * gE[1] + Hi[5] * gE[2];
+        ves[3 * tid] = Hi[0] * gE[0] + Hi[1] * gE[1] + Hi[2] * gE[2];
+        ves[3 * tid + 1] = Hi[1] * gE[0] + Hi[3] * gE[1] + Hi[4] * gE[2];
+        ves[3 * tid + 2] = Hi[2] * gE[0] + Hi[4] * gE[1] + Hi[5] * gE[2];
       }
       if (a.nx > 0) {  // free intrinsics / depth columns staged by phase b1: a warp per track, disjoint from the gathered columns
         for (int k = wib; k < kc; k += NW) {
           const TTrk tk = a.ttrk[trk0 + k];
-          double* G = Gs + (size_t)k * gstride;
+          double* G = Gt + 3 * k;
           for (int i = 0; i < tk.n; i++) {
             const int nxi = rec[tk.q0 + i].nx;
             const double* X = Xs + (size_t)(tk.q0 + i) * 4 * a.nx;
             for (int kk = lane; kk < nxi; kk += 32) {
               const int l2 = (int)X[4 * kk + 3];
               const double sc = cs[l2];
-              G[3 * l2] += X[4 * kk] * sc; G[3 * l2 + 1] += X[4 * kk + 1] * sc; G[3 * l2 + 2] += X[4 * kk + 2] * sc;
+              double* g = G + (size_t)l2 * KK;
+              g[0] += X[4 * kk] * sc; g[1] += X[4 * kk + 1] * sc; g[2] += X[4 * kk + 2] * sc;
             }
             __syncwarp();
           }
         }
       }
+      TPROF(2);
       __syncthreads();
-      // ---- phase b3: Y = G Hinv ----
-      for (int i = tid; i < kc * L8; i += NT) {
-        const int k = i / L8, l = i - k * L8;
-        const double* g = Gs + (size_t)k * gstride + 3 * l;
-        const double* Hi = His + 6 * k;
-        double* y = Ys + (size_t)k * gstride + 3 * l;
-        const double g0 = g[0], g1 = g[1], g2 = g[2];
-        y[0] = Hi[0] * g0 + Hi[1] * g1 + Hi[2] * g2;
-        y[1] = Hi[1] * g0 + Hi[3] * g1 + Hi[4] * g2;
-        y[2] = Hi[2] * g0 + Hi[4] * g1 + Hi[5] * g2;
-      }
-      __syncthreads();
-      // ---- phase c: register patches += Y G' over the staged tracks ----
-      if (worker) {
-        for (int k = 0; k < kc; k++) {
-          const double2* yp = reinterpret_cast<const double2*>(Ys + ((size_t)k * a.L8max + PR * bi) * 3);
-          const double2* gp = reinterpret_cast<const double2*>(Gs + ((size_t)k * a.L8max + 4 * bj) * 3);
-          double y[3 * PR], g[12];
-#pragma unroll
-          for (int i = 0; i < 3 * PR / 2; i++) { double2 tmp = yp[i]; y[2 * i] = tmp.x; y[2 * i + 1] = tmp.y; }
-#pragma unroll
-          for (int i = 0; i < 6; i++) { double2 tmp = gp[i]; g[2 * i] = tmp.x; g[2 * i + 1] = tmp.y; }
-#pragma unroll
-          for (int i = 0; i < PR; i++)
-#pragma unroll
-            for (int j = 0; j < 4; j++)
-              acc[i][j] = fma(y[3 * i], g[3 * j], fma(y[3 * i + 1], g[3 * j + 1], fma(y[3 * i + 2], g[3 * j + 2], acc[i][j])));
-        }
-      }
-      if (tid < L8) {
-        for (int k = 0; k < kc; k++) {
-          const double* gp = Gs + ((size_t)k * a.L8max + tid) * 3;
-          const double* ve = ves + 4 * k;
-          rhs_acc = fma(gp[0], ve[0], fma(gp[1], ve[1], fma(gp[2], ve[2], rhs_acc)));
+      TPROF(3);
+      // ---- phase b3: Y = G Hinv and rhs += G Hinv E'r (a warp per row of Gt, lanes over the staged tracks);
+      //      lane j of warp w keeps the rhs entry of row w + NW j ----
+      {
+        int j = 0;
+        for (int l = wib; l < L8; l += NW, j++) {
+          double part = 0;
+          for (int k = lane; k < kc; k += 32) {
+            const double* g = Gt + (size_t)l * KK + 3 * k;
+            double* y = Yt + (size_t)l * KK + 3 * k;
+            const double g0 = g[0], g1 = g[1], g2 = g[2];
+            const double h0 = His[k], h1 = His[K + k], h2 = His[2 * K + k], h3 = His[3 * K + k], h4 = His[4 * K + k], h5 = His[5 * K + k];
+            y[0] = h0 * g0 + h1 * g1 + h2 * g2;
+            y[1] = h1 * g0 + h3 * g1 + h4 * g2;
+            y[2] = h2 * g0 + h4 * g1 + h5 * g2;
+            part = fma(g0, ves[3 * k], fma(g1, ves[3 * k + 1], fma(g2, ves[3 * k + 2], part)));
+          }
+          part = warp_sum(part);
+          if (lane == j) rhs_acc += part;
         }
       }
       __syncthreads();
+      TPROF(4);
+      // ---- phase c: C += Yt Gt' on the FP64 tensor cores, K dimension = 3 kc (padded with zero columns of Gt) ----
+      if (ns > 0) {
+        const int kend = (3 * kc + 3) & ~3;
+        const double* ybase = Yt + (size_t)gid * KK + tig;
+        const double* gbase = Gt + (size_t)gid * KK + tig;
+        for (int k0 = 0; k0 < kend; k0 += 4) {
+          int bi = bi0, bj = bj0;
+          double av = ybase[(size_t)(8 * bi) * KK + k0];
+#pragma unroll
+          for (int sl = 0; sl < MAXS; sl++) {
+            if (sl < ns) {
+              const double bv = gbase[(size_t)(8 * bj) * KK + k0];
+              dmma884(acc[sl][0], acc[sl][1], av, bv);
+              if (++bj == nb8) { bi++; bj = bi; if (sl + 1 < ns) av = ybase[(size_t)(8 * bi) * KK + k0]; }
+            }
+          }
+        }
+      }
+      TPROF(5);
+      __syncthreads();
+      TPROF(6);
     }
     // ---- flush: local column -> reduced column; window poses are consecutive pose blocks ----
-    if (worker) {
+    {
+      int bi = bi0, bj = bj0;
 #pragma unroll
-      for (int i = 0; i < PR; i++)
+      for (int sl = 0; sl < MAXS; sl++) {
+        if (sl < ns) {
 #pragma unroll
-        for (int j = 0; j < 4; j++) {
-          const int li = PR * bi + i, lj = 4 * bj + j;
-          const double val = acc[i][j];
-          if (li > lj || lj >= Lt || val == 0.0) continue;
-          const int gi = li < 7 * Wt ? 7 * w0 + li : S.npc + (li - 7 * Wt);
-          const int gj = lj < 7 * Wt ? 7 * w0 + lj : S.npc + (lj - 7 * Wt);
-          addS(S, gi, gj, -val);
+          for (int e = 0; e < 2; e++) {
+            const int li = 8 * bi + gid, lj = 8 * bj + 2 * tig + e;
+            const double val = acc[sl][e];
+            if (li <= lj && lj < Lt && val != 0.0) {
+              const int gi = li < 7 * Wt ? 7 * w0 + li : S.npc + (li - 7 * Wt);
+              const int gj = lj < 7 * Wt ? 7 * w0 + lj : S.npc + (lj - 7 * Wt);
+              addS(S, gi, gj, -val);
+            }
+          }
+          if (++bj == nb8) { bi++; bj = bi; }
         }
+      }
     }
-    if (tid < Lt && rhs_acc != 0.0) {
-      const int gi = tid < 7 * Wt ? 7 * w0 + tid : S.npc + (tid - 7 * Wt);
-      atomicAdd(S.rhs + gi, -rhs_acc);
+    {
+      const int l = wib + NW * lane;  // the row whose rhs entry this lane accumulated in phase b3
+      if (l < Lt && rhs_acc != 0.0) {
+        const int gi = l < 7 * Wt ? 7 * w0 + l : S.npc + (l - 7 * Wt);
+        atomicAdd(S.rhs + gi, -rhs_acc);
+      }
     }
   }
   cost_acc = warp_sum(cost_acc);
   if (lane == 0 && cost_acc != 0.0) atomicAdd(a.b.cost, cost_acc);
+#ifdef MVBA_TILE_PROFILE
+  TPROF(7);
+  if (tid == 0) for (int i = 0; i < 8; i++) atomicAdd(&g_tile_prof[i], (unsigned long long)prof_[i]);
+#endif
 }
 
 }  // namespace mvba

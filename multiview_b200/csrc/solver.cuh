@@ -267,13 +267,11 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
     s->grid_cam = std::max(1, std::min(s->nchunks, h->sm_count * std::max(occ_cam, 1)));
   }
   {  // ---- pass B fast path: window tiles ----
-    // one register patch per thread, 512 threads: 4x4 patches up to L8 = 120, 8x4 patches up to L8 = 176
+    // 16 warps x <= 16 accumulator blocks of 8x8 cover the upper block triangle up to L8 = 176 local columns
     int maxspan = 0;
     for (int p = 0; p < v.P; p++) if (trk_any[p]) maxspan = std::max(maxspan, (int)trk_span[p]);
-    const int cap4 = (120 - s->B) / 7, cap8 = (176 - s->B) / 7;
-    int W = maxspan + 2;
-    s->tile_pr = 4;
-    if (W > cap4) { s->tile_pr = 8; W = std::min(W, cap8); }
+    const int capw = (176 - s->B) / 7;
+    int W = std::min(maxspan + 2, capw);
     if (s->B > 176 || W < 0) W = -1;  // nothing fits: every track takes the generic kernel
     std::vector<int32_t> order, fb;
     for (int p = 0; p < v.P; p++) if (trk_any[p]) { if (W >= 0 && trk_span[p] <= W && trk_items[p] <= 32) order.push_back(p); else fb.push_back(p); }
@@ -309,24 +307,26 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
     }
     s->tile_nx = nx;
     {
-      const size_t per_item = sizeof(TRec) + (size_t)32 * nx;
-      const size_t per_trk = (size_t)s->tile_L8max * 48 + 80;
-      const size_t avail = (size_t)dev_smem - 2048 - (size_t)s->tile_L8max * 8;
-      // mean residual blocks per track decides how the budget is split between tracks and staged blocks
+      // the largest K (tracks per round) whose staging fits, with room for ~1.15 x the mean number of blocks per track
       double mean_items = 1.0;
       { double tot = 0; for (int p : order) tot += trk_items[p]; if (!order.empty()) mean_items = std::max(1.0, tot / order.size()); }
-      int K = (int)std::min<double>(32.0, (double)avail / ((double)per_trk + 1.15 * mean_items * (double)per_item));
-      K = std::max(1, K);
-      size_t icap = (avail - (size_t)K * per_trk) / per_item;
-      icap = std::min<size_t>(icap, 511);
-      if (icap < 32) { K = 1; icap = std::min<size_t>(511, (avail - per_trk) / per_item); }
-      if (icap < 32) return fail(MVBA_EINVAL, "mvba: tile staging does not fit shared memory");
-      s->tile_K = K; s->tile_icap = (int)icap;
+      int K = 32, icap = 0;  // phase b3 maps the staged tracks to the lanes of a warp
+      for (; K >= 1; K--) {
+        icap = (int)std::min<double>(511.0, std::max(32.0, std::ceil(1.15 * mean_items * K)));
+        if (tile_smem(K, icap, nx, s->tile_L8max) + 1024 <= (size_t)dev_smem) break;
+      }
+      if (K < 1) return fail(MVBA_EINVAL, "mvba: tile staging does not fit shared memory");
+      while (icap < 511 && tile_smem(K, icap + 1, nx, s->tile_L8max) + 1024 <= (size_t)dev_smem && icap < 2 * mean_items * K) icap++;
+      s->tile_K = K; s->tile_icap = icap;
     }
     s->smem_tile = tile_smem(s->tile_K, s->tile_icap, nx, s->tile_L8max);
-    if (s->smem_tile > (size_t)dev_smem) return fail(MVBA_EINVAL, "mvba: tile staging does not fit shared memory");
+    {  // accumulator blocks per warp: upper block triangle of the widest window over 16 warps
+      const int nb8 = s->tile_L8max / 8, per = (nb8 * (nb8 + 1) / 2 + 15) / 16;
+      s->tile_pr = per <= 4 ? 4 : per <= 8 ? 8 : 16;
+    }
     if (s->tile_pr == 4) MVBA_CUDA(cudaFuncSetAttribute(tile_kernel<512, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_tile));
-    else MVBA_CUDA(cudaFuncSetAttribute(tile_kernel<512, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_tile));
+    else if (s->tile_pr == 8) MVBA_CUDA(cudaFuncSetAttribute(tile_kernel<512, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_tile));
+    else MVBA_CUDA(cudaFuncSetAttribute(tile_kernel<512, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_tile));
     // ---- static round tables ----
     std::vector<int32_t> tile_round0{0}, round_trk0{0}, round_blk0{0}, round_grp0{0};
     std::vector<TBlk> blk; std::vector<TTrk> ttrk; std::vector<TGrp> grp; std::vector<uint16_t> con;
@@ -368,8 +368,11 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
           for (int64_t j = h->h_trk_pt0[p]; j < h->h_trk_pt0[p + 1]; j++) { blk.push_back(TBlk{(int32_t)j, 4}); q++; }
           for (const Key& key : keys) {
             if (con.size() >= ((size_t)1 << 32) - 64) return fail(MVBA_EINVAL, "mvba: gather table too large");
-            grp.push_back(TGrp{(uint32_t)con.size(), (uint16_t)key.lcol, (uint8_t)k, (uint8_t)(key.c.size() | (key.single ? 0x80 : 0))});
-            con.insert(con.end(), key.c.begin(), key.c.end());
+            TGrp g{};
+            g.over0 = (uint32_t)con.size(); g.lcol = (uint16_t)key.lcol; g.k = (uint8_t)k;
+            g.ncon = (uint8_t)(key.c.size() | (key.single ? 0x80 : 0));
+            for (size_t u = 0; u < key.c.size(); u++) { if (u < 4) g.c[u] = key.c[u]; else con.push_back(key.c[u]); }
+            grp.push_back(g);
           }
         }
         ti += kc;
@@ -379,7 +382,7 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
     }
     s->nrounds = (int)round_trk0.size() - 1;
     if (con.empty()) con.push_back(0);
-    if (grp.empty()) grp.push_back(TGrp{0, 0, 0, 0});
+    if (grp.empty()) grp.push_back(TGrp{});
     if (blk.empty()) blk.push_back(TBlk{0, 0});
     if (ttrk.empty()) ttrk.push_back(TTrk{0, 0, 0});
     MVBA_CUDA(s->tile_round0.upload(tile_round0)); MVBA_CUDA(s->round_trk0.upload(round_trk0)); MVBA_CUDA(s->round_blk0.upload(round_blk0));

@@ -52,7 +52,8 @@ inline int run_build(mvba_problem* h, const mvba_solve_options& o, double radius
       ta.blk = s->t_blk.p; ta.ttrk = s->t_trk.p; ta.grp = s->t_grp.p; ta.con = s->t_con.p;
       ta.ntiles = s->ntiles; ta.K = s->tile_K; ta.icap = s->tile_icap; ta.nx = s->tile_nx; ta.L8max = s->tile_L8max; ta.coef = h->d_coef.p;
       if (s->tile_pr == 4) tile_kernel<512, 4><<<s->grid_tile, 512, s->smem_tile, h->stream>>>(v, ta, s->R);
-      else tile_kernel<512, 8><<<s->grid_tile, 512, s->smem_tile, h->stream>>>(v, ta, s->R);
+      else if (s->tile_pr == 8) tile_kernel<512, 8><<<s->grid_tile, 512, s->smem_tile, h->stream>>>(v, ta, s->R);
+      else tile_kernel<512, 16><<<s->grid_tile, 512, s->smem_tile, h->stream>>>(v, ta, s->R);
       h->launches++;
     }
     if (s->nfallback > 0) {
@@ -63,6 +64,20 @@ inline int run_build(mvba_problem* h, const mvba_solve_options& o, double radius
     }
   }
   if (s->tm) s->tm->end();
+#ifdef MVBA_TILE_PROFILE
+  if (mode == 0 && s->ntiles > 0) {
+    unsigned long long pr[8], z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    cudaStreamSynchronize(h->stream);
+    cudaMemcpyFromSymbol(pr, g_tile_prof, sizeof(pr));
+    cudaMemcpyToSymbol(g_tile_prof, z, sizeof(z));
+    double tot = 0; for (int i = 0; i < 8; i++) tot += (double)pr[i];
+    std::printf("tile prof (thread 0 of each CTA, %% of cycles): b1 %.1f | bar %.1f | b2 %.1f | bar %.1f | b3+bar %.1f | c %.1f | bar %.1f | flush+tile setup %.1f  (Mcycles/CTA %.2f)\n",
+                100 * pr[0] / tot, 100 * pr[1] / tot, 100 * pr[2] / tot, 100 * pr[3] / tot, 100 * pr[4] / tot, 100 * pr[5] / tot, 100 * pr[6] / tot, 100 * pr[7] / tot,
+                tot / s->grid_tile * 1e-6);
+    static bool once = false;
+    if (!once) { once = true; std::printf("tile plan: nt %d pr %d K %d icap %d L8max %d ntiles %d nrounds %d nfallback %d grid %d smem %zu B %d\n", s->tile_nt, s->tile_pr, s->tile_K, s->tile_icap, s->tile_L8max, s->ntiles, s->nrounds, s->nfallback, s->grid_tile, s->smem_tile, s->B); }
+  }
+#endif
   s->build_launches++;
   MVBA_CUDA(cudaGetLastError());
   return allreduce(h, s->red.p, s->red_n, 8, 0);
