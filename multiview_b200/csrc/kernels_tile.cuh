@@ -209,7 +209,7 @@ __device__ __forceinline__ void tile_gather(const TileArgs& ta, const TGrp gr, i
 // D(8x8) += A(8x4) B(4x8) on the FP64 tensor cores: a = A[lane/4][lane%4], b = B[lane%4][lane/4],
 // c0, c1 = C[lane/4][2 (lane%4) + {0, 1}].
 __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
-  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+  asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
 
 #ifdef MVBA_TILE_PROFILE
@@ -361,6 +361,7 @@ __global__ void __launch_bounds__(NT, 1) tile_kernel(View v, TileArgs a, Reduced
         const int kend = (3 * kc + 3) & ~3;
         const double* ybase = Yt + (size_t)gid * KK + tig;
         const double* gbase = Gt + (size_t)gid * KK + tig;
+#pragma unroll(MAXS <= 4 ? 4 : MAXS <= 8 ? 2 : 1)
         for (int k0 = 0; k0 < kend; k0 += 4) {
           int bi = bi0, bj = bj0;
           double av = ybase[(size_t)(8 * bi) * KK + k0];
