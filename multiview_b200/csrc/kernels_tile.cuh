@@ -77,18 +77,21 @@ __host__ __device__ inline size_t tile_smem(int K, int icap, int nx, int L8max) 
 
 // Phase b1: one thread evaluates one residual block.  Nothing here is Jacobi-scaled on the f side (phase b2 scales
 // whole columns once); E carries the landmark scaling.
-__device__ inline double tile_eval(const View& v, const BuildArgs& a, const Reduced& S, const TBlk bk, int Wt,
-                                   TRec& rec, double* X, double* jd) {
+// HAS_X = false (no free intrinsics / depth columns anywhere): no distortion Jacobian, no dynamically indexed
+// column loop, so the block's Item stays in registers.
+template <bool HAS_X>
+__device__ __forceinline__ double tile_eval(const View& v, const BuildArgs& a, const Reduced& S, const TBlk bk, int Wt,
+                                            TRec& rec, double* X, double* jd) {
   Item it;
   const int kind = bk.kind;
   const int64_t idx = bk.idx;
-  if (kind == 0) eval_cam<true>(v, a.x, a.tab, idx, it, jd, jd + MVBA_MAXDZ);
+  if (kind == 0) eval_cam<true>(v, a.x, a.tab, idx, it, HAS_X ? jd : nullptr, HAS_X ? jd + MVBA_MAXDZ : nullptr);
   else if (kind == 1) eval_depth(v, a.x, a.tab, a.dtab, MVBA_BLOCK_DEPTH_TRI, idx, it);
   else if (kind == 2) eval_depth(v, a.x, a.tab, a.dtab, MVBA_BLOCK_DEPTH_MESH, idx, it);
   else eval_prior(v, a.x, idx, it);
   const int p = it.pid;
-  double s = 0;
-  for (int k = 0; k < it.nr; k++) s += it.r[k] * it.r[k];
+  double s = it.r[0] * it.r[0] + it.r[1] * it.r[1];
+  if (it.nr == 3) s += it.r[2] * it.r[2];
   double hr, sr;
   cauchy(it.loss_a, s, &hr, &sr);
   double se[3] = {1, 1, 1};
@@ -120,12 +123,12 @@ __device__ inline double tile_eval(const View& v, const BuildArgs& a, const Redu
   for (int b = 0; b < 3; b++)
 #pragma unroll
     for (int aa = 0; aa < 3; aa++) {
-      double t = 0;
-      for (int r = 0; r < it.nr; r++) t += it.A[3 * r + aa] * Es[3 * r + b];
+      double t = it.A[aa] * Es[b] + it.A[3 + aa] * Es[3 + b];  // every block kind has at least two rows
+      if (it.nr == 3) t += it.A[6 + aa] * Es[6 + b];
       rec.M[3 * aa + b] = sr * t;
     }
   // free non-pose columns (focal, centre, distortion | depth transform, scale): direct J'E with the target column
-  if (sd.c_focal >= 0 || sd.c_center >= 0 || sd.c_dist >= 0 || sd.c_d2i >= 0 || sd.c_scale >= 0) {
+  if (HAS_X && (sd.c_focal >= 0 || sd.c_center >= 0 || sd.c_dist >= 0 || sd.c_d2i >= 0 || sd.c_scale >= 0)) {
     const int vw = item_vwidth(v, it);
     int n = 0;
     for (int vc = MVBA_VPOSE; vc < vw; vc++) {
@@ -135,8 +138,8 @@ __device__ inline double tile_eval(const View& v, const BuildArgs& a, const Redu
       item_jcol(v, it, a.tab, a.dtab, vc, jd, jd + MVBA_MAXDZ, col);
 #pragma unroll
       for (int b = 0; b < 3; b++) {
-        double x = 0;
-        for (int r = 0; r < it.nr; r++) x += col[r] * Es[3 * r + b];
+        double x = col[0] * Es[b] + col[1] * Es[3 + b];
+        if (it.nr == 3) x += col[2] * Es[6 + b];
         X[4 * n + b] = sr * x;
       }
       X[4 * n + 3] = (double)(7 * Wt + (gc - S.npc));
@@ -165,10 +168,18 @@ __device__ __forceinline__ void gather_term(const TRec& r, int role, int row, co
 // Phase b2: row `row` of group `gr` of G = F'E for one staged track, gathered over the group's contributors and
 // Jacobi-scaled.  G points at the track's three columns of Gt (row stride KK).  The coefficient loads (L2) of the four inline
 // contributors are issued together.
-__device__ __forceinline__ void tile_gather(const TileArgs& ta, const TGrp gr, int row, const TRec* __restrict__ rec,
-                                            const double* __restrict__ cs, double* __restrict__ G, int KK) {
-  const bool single = (gr.ncon & 0x80) != 0;
-  const int ncon = gr.ncon & 0x7f;
+// (The group record is decoded from its raw 16 bytes with shifts: a TGrp object indexed by `u` would live in local memory.)
+__device__ __forceinline__ unsigned grp_con(const int4& raw, int u) {
+  const unsigned w = u < 2 ? (unsigned)raw.z : (unsigned)raw.w;
+  return (w >> (16 * (u & 1))) & 0xffffu;
+}
+__device__ __forceinline__ void tile_gather(const TileArgs& ta, const int4 raw, int row, const TRec* __restrict__ rec,
+                                            const double* __restrict__ cs, double* __restrict__ Gt, int KK) {
+  const unsigned over0 = (unsigned)raw.x;
+  const int lcol = raw.y & 0xffff, ktrk = (raw.y >> 16) & 0xff, nc = ((unsigned)raw.y >> 24);
+  double* G = Gt + 3 * ktrk;
+  const bool single = (nc & 0x80) != 0;
+  const int ncon = nc & 0x7f;
   if (row >= (single ? 1 : 7)) return;
   double o[3] = {0, 0, 0};
   int c = 0;
@@ -178,7 +189,7 @@ __device__ __forceinline__ void tile_gather(const TileArgs& ta, const TGrp gr, i
     const TRec* rp[4];
 #pragma unroll
     for (int u = 0; u < 4; u++) {
-      const unsigned cb = gr.c[u];
+      const unsigned cb = grp_con(raw, u);
       rp[u] = rec + (cb >> 2); role[u] = cb & 3;
       if (u < ncon) {
         const double* p = ta.coef[rp[u]->cid].c[7 * role[u] + row];
@@ -191,7 +202,7 @@ __device__ __forceinline__ void tile_gather(const TileArgs& ta, const TGrp gr, i
     c = 4;
   }
   for (; c < ncon; c++) {
-    const unsigned cb = c < 4 ? gr.c[c] : __ldg(ta.con + gr.over0 + (c - 4));
+    const unsigned cb = c < 4 ? grp_con(raw, c) : __ldg(ta.con + over0 + (c - 4));
     const TRec& r = rec[cb >> 2];
     const int rl = cb & 3;
     const double* p = ta.coef[r.cid].c[rl == 3 ? 21 : 7 * rl + row];
@@ -200,7 +211,7 @@ __device__ __forceinline__ void tile_gather(const TileArgs& ta, const TGrp gr, i
     if (rl == 3) { e3[0] = __ldg(p + 3); e3[1] = __ldg(p + 4); e3[2] = __ldg(p + 5); }
     gather_term(r, rl, row, c3, e3, o);
   }
-  const int l = gr.lcol + row;
+  const int l = lcol + row;
   const double sc = cs[l];
   double* g = G + (size_t)l * KK;
   g[0] = o[0] * sc; g[1] = o[1] * sc; g[2] = o[2] * sc;
@@ -267,8 +278,13 @@ __global__ void __launch_bounds__(NT, 1) tile_kernel(View v, TileArgs a, Reduced
       const int blk0 = a.round_blk0[rd], nit = a.round_blk0[rd + 1] - blk0;
       const int grp0 = a.round_grp0[rd], ngrp = a.round_grp0[rd + 1] - grp0;
       // ---- phase b1: one thread per residual block; everyone clears Gt ----
-      for (int q = tid; q < nit; q += NT)
-        cost_acc += tile_eval(v, a.b, S, a.blk[blk0 + q], Wt, rec[q], Xs + (size_t)q * 4 * a.nx, jd);
+      if (a.nx > 0) {
+        for (int q = tid; q < nit; q += NT)
+          cost_acc += tile_eval<true>(v, a.b, S, a.blk[blk0 + q], Wt, rec[q], Xs + (size_t)q * 4 * a.nx, jd);
+      } else {
+        for (int q = tid; q < nit; q += NT)
+          cost_acc += tile_eval<false>(v, a.b, S, a.blk[blk0 + q], Wt, rec[q], nullptr, nullptr);
+      }
       {
         double2* gz = reinterpret_cast<double2*>(Gt);
         const int nz = L8 * KK / 2;
@@ -285,9 +301,7 @@ __global__ void __launch_bounds__(NT, 1) tile_kernel(View v, TileArgs a, Reduced
         while (i < 8 * ngrp) {
           const int inext = i + NT;
           const int4 rawn = inext < 8 * ngrp ? __ldg(gtab + (inext >> 3)) : make_int4(0, 0, 0, 0);
-          TGrp gr;
-          *reinterpret_cast<int4*>(&gr) = raw;
-          tile_gather(a, gr, i & 7, rec, cs, Gt + 3 * gr.k, KK);
+          tile_gather(a, raw, i & 7, rec, cs, Gt, KK);
           raw = rawn; i = inext;
         }
       }

@@ -48,7 +48,9 @@ def test_lm_trajectory_and_converged_state(name, oracle_lib, product_lib):
     # depth_mesh floats depth_to_image + scale + rig at once: the gauge is only weakly held, so round-off
     # differences grow along it after a few iterations; it is compared while both are on the same path.
     iters = ITERS.get(name, 12)
-    so, lo, xo = _run(oracle_lib, "oracle_", pr, snap, iters, jac_mode=1)
+    # one oracle thread: its OpenMP reductions are otherwise order-dependent, and an iteration with 20+ CG steps can
+    # flip the Q-based stopping test on that round-off alone (seen as a 1.5e-6 cost difference at iteration 9 of "offsets")
+    so, lo, xo = _run(oracle_lib, "oracle_", pr, snap, iters, jac_mode=1, num_threads=1)
     sg, lg, xg = _run(product_lib, "mvba_", pr, snap, iters)
     assert sg.num_kernel_launches > 0
     assert abs(sg.initial_cost - so.initial_cost) <= 1e-9 * so.initial_cost
