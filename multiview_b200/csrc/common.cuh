@@ -97,6 +97,12 @@ __device__ __forceinline__ void cross3(const double* a, const double* b, double*
   o[2] = a[0] * b[1] - a[1] * b[0];
 }
 
+// D(8x8) += A(8x4) B(4x8) on the FP64 tensor cores: a = A[lane/4][lane%4], b = B[lane%4][lane/4],
+// c0, c1 = C[lane/4][2 (lane%4) + {0, 1}].
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
+  asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+
 // 3x3 symmetric inverse from the 6 unique entries (xx xy xz yy yz zz); returns false when singular.
 __device__ __forceinline__ bool inv_sym3(const double* h, double* o) {
   double c00 = h[3] * h[5] - h[4] * h[4];

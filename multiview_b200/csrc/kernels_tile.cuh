@@ -217,12 +217,6 @@ __device__ __forceinline__ void tile_gather(const TileArgs& ta, const int4 raw, 
   g[0] = o[0] * sc; g[1] = o[1] * sc; g[2] = o[2] * sc;
 }
 
-// D(8x8) += A(8x4) B(4x8) on the FP64 tensor cores: a = A[lane/4][lane%4], b = B[lane%4][lane/4],
-// c0, c1 = C[lane/4][2 (lane%4) + {0, 1}].
-__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
-  asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
-}
-
 #ifdef MVBA_TILE_PROFILE
 __device__ unsigned long long g_tile_prof[8];
 #define TPROF(slot) do { if (tid == 0) { long long now_ = clock64(); prof_[slot] += now_ - tp_; tp_ = now_; } } while (0)

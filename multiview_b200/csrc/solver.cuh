@@ -231,7 +231,9 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
       maxact = std::max(maxact, n);
     }
     if (maxact + 1 > MVBA_CAM_MAXACT) return fail(MVBA_EINVAL, "mvba: one image touches more than 87 free non-landmark columns");
+    // row stride: = 12 (mod 16) doubles when every image fits the 24-column tensor fold (conflict-free DMMA fragment loads)
     s->cam_ldj = ((maxact + 1 + 3) / 4) * 4;
+    if (maxact + 1 <= 24) { s->cam_ldj = ((maxact + 1 + 7) / 8) * 8; while ((s->cam_ldj & 15) != 12) s->cam_ldj += 4; }
     const int64_t target = std::max<int64_t>(256, std::min<int64_t>(4096, nit / std::max(1, 4 * h->sm_count)));
     std::vector<int32_t> ccam, cbeg;
     for (int c = 0; c < v.C; c++) {
@@ -255,12 +257,12 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
   if (s->maxdz > MVBA_MAXDZ) return fail(MVBA_EINVAL, "mvba: distortion block too long");
   MVBA_CUDA(s->camdir.alloc(std::max(v.C, 1))); MVBA_CUDA(s->sensdir.alloc(std::max(v.T, 1)));
   {  // pass A: stage as many blocks per round as ~100 KB allows (two CTAs per SM)
-    const size_t budget = std::min<size_t>((size_t)dev_smem, 100 * 1024) - 3 * MVBA_CAM_MAXACT * 4 - 64;
-    int bi = (int)(budget / ((size_t)3 * s->cam_ldj * 8));
-    bi = std::min(256, (bi / 32) * 32);
-    if (bi < 32) return fail(MVBA_EINVAL, "mvba: pass A staging does not fit shared memory");
-    s->cam_batch = bi;
-    s->smem_cam = cam_pass_smem(bi, s->cam_ldj);
+    const size_t budget = std::min<size_t>((size_t)dev_smem, 112 * 1024) - cam_pass_smem(0, s->cam_ldj);
+    int rows = (int)(budget / ((size_t)s->cam_ldj * 8));
+    rows = std::min(3 * MVBA_CAM_THREADS, (rows / 12) * 12);
+    if (rows < 96) return fail(MVBA_EINVAL, "mvba: pass A staging does not fit shared memory");
+    s->cam_batch = rows;
+    s->smem_cam = cam_pass_smem(rows, s->cam_ldj);
     MVBA_CUDA(cudaFuncSetAttribute(camera_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_cam));
     int occ_cam = 1;
     MVBA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_cam, camera_pass_kernel, MVBA_CAM_THREADS, s->smem_cam));

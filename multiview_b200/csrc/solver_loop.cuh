@@ -37,7 +37,7 @@ inline int run_build(mvba_problem* h, const mvba_solve_options& o, double radius
     CamPassArgs ca{};
     ca.x = h->d_x.p; ca.tab = h->d_tab.p; ca.dtab = h->d_dtab.p; ca.jscale_f = a.jscale_f;
     ca.chunk_cam = s->chunk_cam.p; ca.chunk_beg = s->chunk_beg.p; ca.citems = s->citems.p; ca.nchunks = s->nchunks;
-    ca.batch_items = s->cam_batch; ca.ldj = s->cam_ldj; ca.mode = mode;
+    ca.batch_rows = s->cam_batch; ca.ldj = s->cam_ldj; ca.mode = mode; ca.coef = h->d_coef.p;
     camera_pass_kernel<<<s->grid_cam, MVBA_CAM_THREADS, s->smem_cam, h->stream>>>(v, ca, s->R);
     h->launches++;
   }
