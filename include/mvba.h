@@ -242,6 +242,26 @@ int mvba_solve_options_init(mvba_solve_options* o);
 int mvba_solve(mvba_problem* h, const mvba_solve_options* o, mvba_summary* s,
                mvba_iteration* iterations, int32_t max_iterations_out);
 
+/* ---- per-track steps that run around every pass (device kernels, one thread per track) ----
+ * The handle's observations are the features of the pass; `inlier` is one byte per observation in the
+ * order they were given to mvba_set_observations (the reference's pid_cid_fid_inlier map,
+ * rig_calibrator.cc:1528-1532).  A flag that is 0 on entry is skipped and stays 0. */
+/* multiViewTriangulation (rig_calibrator/src/interest_point.cc:649-722): undistorts every inlier feature
+ * (Convert<DISTORTED, UNDISTORTED_C>, camera_model/camera_params.cc:316-355), triangulates each track with
+ * openMVG's 3-pass reweighted linear method (openMVG/multiview/triangulation_nview.cc:87-146) from the
+ * CURRENT camera parameters and writes xyz[3 P]; tracks with fewer than two inlier rays or a non-finite
+ * result lose all their features and keep the xyz they came in with. */
+int mvba_triangulate(mvba_problem* h, uint8_t* inlier, double* xyz);
+/* flagOutliersByTriAngleAndReprojErr (rig_calibrator/bin/rig_calibrator.cc:1045-1154) at the CURRENT
+ * parameters: tracks whose largest ray convergence angle is below min_triangulation_angle (degrees) lose
+ * all features, then features with a pixel residual norm above max_reprojection_error are dropped.
+ * counts (may be NULL): features seen / removed by the angle step, seen / removed by the reprojection step. */
+int mvba_flag_outliers(mvba_problem* h, double min_triangulation_angle, double max_reprojection_error,
+                       uint8_t* inlier, int64_t counts[4]);
+/* flagOutlierByExclusionDist (rig_calibrator.cc:1003-1038): features outside the centred crop box
+ * (distorted_crop_size) of their sensor's image (image_size); both arrays hold 2 values per sensor. */
+int mvba_flag_exclusion(mvba_problem* h, const double* image_size, const double* crop_size, uint8_t* inlier);
+
 /* ---- measurement hooks (bench.py); device-resident inputs, CUDA-event timed ---- */
 /* Uploads parameters and keeps them resident. */
 int mvba_upload(mvba_problem* h);

@@ -44,7 +44,7 @@ __host__ __device__ inline size_t cam_pass_smem(int batch_rows, int ldj) {
   return ((size_t)(batch_rows + 4) * ldj + 72 + MVBA_CAM_MAXACT) * 8 + 3 * MVBA_CAM_MAXACT * 4 + 16;
 }
 
-__global__ void __launch_bounds__(MVBA_CAM_THREADS) camera_pass_kernel(View v, CamPassArgs a, Reduced S) {
+__global__ void __launch_bounds__(MVBA_CAM_THREADS, 2) camera_pass_kernel(View v, CamPassArgs a, Reduced S) {
   extern __shared__ double smem_d[];
   double* Js = smem_d;
   double* ccoef = Js + (size_t)(a.batch_rows + 4) * a.ldj;   // 23 x 3

@@ -6,6 +6,7 @@
 #include "handle.cuh"
 #include "setup.cuh"
 #include "solver.cuh"
+#include "kernels_tracks.cuh"
 
 namespace mvba {
 thread_local std::string g_last_error;
@@ -257,6 +258,72 @@ int mvba_solve(mvba_problem* h, const mvba_solve_options* o, mvba_summary* s, mv
 int mvba_bench_build(mvba_problem* h, int32_t repeats, float* ms_total) {
   int rc = ready(h); if (rc) return rc;
   return solver_bench_build(h, repeats, ms_total);
+}
+
+// ---- per-track steps around a pass ----
+static int tracks_begin(mvba_problem* h, const uint8_t* inlier, mvba::DBuf<uint8_t>& d_in) {
+  int rc = ready(h); if (rc) return rc;
+  if (!inlier) return fail(MVBA_EINVAL, "mvba: null inlier array");
+  rc = upload_params(h); if (rc) return rc;
+  MVBA_CUDA(cudaMemsetAsync(h->d_err.p, 0, sizeof(int), h->stream));
+  run_prep(h, h->d_x.p);
+  MVBA_CUDA(d_in.alloc((size_t)std::max<int64_t>(h->view.N, 1)));
+  if (h->view.N > 0) MVBA_CUDA(cudaMemcpyAsync(d_in.p, inlier, (size_t)h->view.N, cudaMemcpyHostToDevice, h->stream));
+  return MVBA_OK;
+}
+
+int mvba_triangulate(mvba_problem* h, uint8_t* inlier, double* xyz) {
+  mvba::DBuf<uint8_t> d_in; mvba::DBuf<double> d_xyz;
+  int rc = tracks_begin(h, inlier, d_in); if (rc) return rc;
+  if (!xyz) return fail(MVBA_EINVAL, "mvba_triangulate: null xyz array");
+  const View& v = h->view;
+  if (v.P == 0) return MVBA_OK;
+  MVBA_CUDA(d_xyz.alloc((size_t)3 * v.P));
+  MVBA_CUDA(cudaMemcpyAsync(d_xyz.p, xyz, sizeof(double) * 3 * v.P, cudaMemcpyHostToDevice, h->stream));
+  const int grid = std::max(1, std::min((v.P + 127) / 128, h->sm_count * 16));
+  triangulate_kernel<<<grid, 128, 0, h->stream>>>(v, h->d_x.p, h->d_tab.p, d_in.p, d_xyz.p);
+  h->launches++;
+  MVBA_CUDA(cudaGetLastError());
+  MVBA_CUDA(cudaMemcpyAsync(xyz, d_xyz.p, sizeof(double) * 3 * v.P, cudaMemcpyDeviceToHost, h->stream));
+  if (v.N > 0) MVBA_CUDA(cudaMemcpyAsync(inlier, d_in.p, (size_t)v.N, cudaMemcpyDeviceToHost, h->stream));
+  return check_device_error(h);
+}
+
+int mvba_flag_outliers(mvba_problem* h, double min_triangulation_angle, double max_reprojection_error, uint8_t* inlier, int64_t counts[4]) {
+  mvba::DBuf<uint8_t> d_in; mvba::DBuf<unsigned long long> d_cnt;
+  int rc = tracks_begin(h, inlier, d_in); if (rc) return rc;
+  const View& v = h->view;
+  MVBA_CUDA(d_cnt.alloc(4)); MVBA_CUDA(d_cnt.zero(h->stream));
+  if (v.P > 0) {
+    const int grid = std::max(1, std::min((v.P + 127) / 128, h->sm_count * 16));
+    flag_angle_reproj_kernel<<<grid, 128, 0, h->stream>>>(v, h->d_x.p, h->d_tab.p, min_triangulation_angle, max_reprojection_error, d_in.p, d_cnt.p);
+    h->launches++;
+    MVBA_CUDA(cudaGetLastError());
+  }
+  unsigned long long c[4] = {0, 0, 0, 0};
+  MVBA_CUDA(cudaMemcpyAsync(c, d_cnt.p, sizeof(c), cudaMemcpyDeviceToHost, h->stream));
+  if (v.N > 0) MVBA_CUDA(cudaMemcpyAsync(inlier, d_in.p, (size_t)v.N, cudaMemcpyDeviceToHost, h->stream));
+  rc = check_device_error(h); if (rc) return rc;
+  if (counts) for (int i = 0; i < 4; i++) counts[i] = (int64_t)c[i];
+  return MVBA_OK;
+}
+
+int mvba_flag_exclusion(mvba_problem* h, const double* image_size, const double* crop_size, uint8_t* inlier) {
+  mvba::DBuf<uint8_t> d_in; mvba::DBuf<double> d_sz;
+  int rc = tracks_begin(h, inlier, d_in); if (rc) return rc;
+  if (!image_size || !crop_size) return fail(MVBA_EINVAL, "mvba_flag_exclusion: null size array");
+  const View& v = h->view;
+  std::vector<double> sz((size_t)4 * v.T);
+  for (int i = 0; i < 2 * v.T; i++) { sz[i] = crop_size[i]; sz[2 * v.T + i] = image_size[i]; }
+  MVBA_CUDA(d_sz.upload(sz));
+  if (v.N > 0) {
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((v.N + 255) / 256, (int64_t)h->sm_count * 16));
+    flag_exclusion_kernel<<<grid, 256, 0, h->stream>>>(v, d_sz.p, d_sz.p + 2 * v.T, d_in.p);
+    h->launches++;
+    MVBA_CUDA(cudaGetLastError());
+    MVBA_CUDA(cudaMemcpyAsync(inlier, d_in.p, (size_t)v.N, cudaMemcpyDeviceToHost, h->stream));
+  }
+  return check_device_error(h);
 }
 
 int mvba_nccl_unique_id(uint8_t id128[128]) { return comm_unique_id(id128); }

@@ -22,6 +22,7 @@
 
 #include "../include/mvba.h"
 #include "functors.h"
+#include "tracks.h"
 
 namespace oracle {
 
@@ -861,5 +862,132 @@ void oracle_world_to_cam(const double* beg, const double* end, const double* r2c
 void oracle_distort(double w, double hgt, int nd, double f, const double* c, const double* dist, const double* u, double* out) {
   oracle::SensorConst s{{w / 2, hgt / 2}, nd}; double dummy = 0;
   oracle::distort_undist_c_to_dist<double>(s, f, c, nd > 0 ? dist : &dummy, u, out);
+}
+
+// ---- per-track steps around a pass; same signatures as the mvba_ entry points ----
+// world_to_cam of the image of CAM block b at the current parameters (calc_world_to_cam_trans, rig_calibrator.cc:362-390).
+static oracle::Aff<double> block_world_to_cam(const Problem& P, const oracle::RBlock& b) {
+  bool ok = true;
+  return oracle::calc_world_to_cam_trans<double>(P.pbs[b.pb[0]].ptr, P.pbs[b.pb[1]].ptr, P.pbs[b.pb[2]].ptr, b.stamps[0], b.stamps[1],
+                                                 P.pbs[b.pb[4]].ptr[0], b.stamps[2], &ok);
+}
+// CAM blocks in observation order (b.src = observation index)
+static std::vector<const oracle::RBlock*> cam_blocks(const Problem& P) {
+  std::vector<const oracle::RBlock*> out((size_t)P.nobs, nullptr);
+  for (auto& b : P.rbs) if (b.kind == MVBA_BLOCK_CAM) out[(size_t)b.src] = &b;
+  return out;
+}
+// multiViewTriangulation, interest_point.cc:649-722
+int oracle_triangulate(void* h, uint8_t* inlier, double* xyz) {
+  Problem* P = (Problem*)h; ensure(P);
+  auto cb = cam_blocks(*P);
+  int64_t i = 0;
+  while (i < P->nobs) {
+    const int pid = P->opid[i];
+    int64_t j = i;
+    while (j < P->nobs && P->opid[j] == pid) j++;
+    std::vector<oracle::View34> views;
+    for (int64_t q = i; q < j; q++) {
+      if (!inlier[q]) continue;
+      const oracle::RBlock& b = *cb[q];
+      const oracle::SensorConst& s = P->sensors[b.sensor];
+      const double f = P->pbs[b.pb[5]].ptr[0];
+      const double* c = P->pbs[b.pb[6]].ptr;
+      double dummy = 0;
+      const double* dist = s.nd > 0 ? P->pbs[b.pb[7]].ptr : &dummy;
+      const double dc[2] = {b.meas[0] - s.half[0], b.meas[1] - s.half[1]};  // Convert<DISTORTED, DISTORTED_C>
+      oracle::View34 v;
+      oracle::undistort_centered(s, f, c, dist, dc, v.p);
+      oracle::Aff<double> w2c = block_world_to_cam(*P, b);
+      for (int a = 0; a < 3; a++) {  // P = K [R | t], K = diag(f, f, 1)   (P_From_KRt)
+        const double k = a < 2 ? f : 1.0;
+        for (int e = 0; e < 3; e++) v.P[a][e] = k * w2c.m[a][e];
+        v.P[a][3] = k * w2c.t[a];
+      }
+      views.push_back(v);
+    }
+    if (views.size() < 2) {
+      for (int64_t q = i; q < j; q++) inlier[q] = 0;
+    } else {
+      double X[3];
+      oracle::triangulate_views(views, X);
+      for (int a = 0; a < 3; a++) xyz[3 * (size_t)pid + a] = X[a];
+      if (!std::isfinite(X[0]) || !std::isfinite(X[1]) || !std::isfinite(X[2]))
+        for (int64_t q = i; q < j; q++) inlier[q] = 0;
+    }
+    i = j;
+  }
+  return 0;
+}
+// flagOutliersByTriAngleAndReprojErr, rig_calibrator.cc:1045-1154 (residuals = evalResiduals at the current parameters)
+int oracle_flag_outliers(void* h, double min_triangulation_angle, double max_reprojection_error, uint8_t* inlier, int64_t counts[4]) {
+  Problem* P = (Problem*)h; ensure(P);
+  auto cb = cam_blocks(*P);
+  std::vector<double> res((size_t)P->nres);
+  oracle::evaluate(*P, false, res.data());
+  int64_t n_total = 0, n_angle = 0;
+  auto centre = [&](int64_t q, double c[3]) {  // world_to_cam^-1 * 0
+    oracle::Aff<double> inv = oracle::aff_inverse(block_world_to_cam(*P, *cb[q]));
+    const double z[3] = {0, 0, 0};
+    oracle::aff_apply(inv, z, c);
+  };
+  int64_t i = 0;
+  while (i < P->nobs) {
+    const int pid = P->opid[i];
+    int64_t j = i;
+    while (j < P->nobs && P->opid[j] == pid) j++;
+    const double* X = P->prm.xyz + 3 * (size_t)pid;
+    double max_angle = 0.0;
+    for (int64_t q1 = i; q1 < j; q1++) {
+      if (!inlier[q1]) continue;
+      n_total++;
+      double c1[3], r1[3];
+      centre(q1, c1);
+      for (int a = 0; a < 3; a++) r1[a] = X[a] - c1[a];
+      double n1 = std::sqrt(r1[0] * r1[0] + r1[1] * r1[1] + r1[2] * r1[2]);
+      if (n1 > 0) for (int a = 0; a < 3; a++) r1[a] /= n1;
+      for (int64_t q2 = i; q2 < j; q2++) {
+        if (P->ocid[q2] <= P->ocid[q1] || !inlier[q2]) continue;
+        double c2[3], r2[3];
+        centre(q2, c2);
+        for (int a = 0; a < 3; a++) r2[a] = X[a] - c2[a];
+        double n2 = std::sqrt(r2[0] * r2[0] + r2[1] * r2[1] + r2[2] * r2[2]);
+        if (n2 > 0) for (int a = 0; a < 3; a++) r2[a] /= n2;
+        double ang = (180.0 / M_PI) * std::acos(r1[0] * r2[0] + r1[1] * r2[1] + r1[2] * r2[2]);
+        if (std::isnan(ang) || std::isinf(ang)) continue;
+        max_angle = std::max(max_angle, ang);
+      }
+    }
+    if (!(max_angle >= min_triangulation_angle))
+      for (int64_t q = i; q < j; q++) if (inlier[q]) { inlier[q] = 0; n_angle++; }
+    i = j;
+  }
+  int64_t n_total2 = 0, n_reproj = 0;
+  for (int64_t q = 0; q < P->nobs; q++) {
+    if (!inlier[q]) continue;
+    n_total2++;
+    const double rx = res[(size_t)cb[q]->row0], ry = res[(size_t)cb[q]->row0 + 1];
+    const bool good = std::sqrt(rx * rx + ry * ry) <= max_reprojection_error;
+    if (!good) { inlier[q] = 0; n_reproj++; }
+  }
+  if (counts) { counts[0] = n_total; counts[1] = n_angle; counts[2] = n_total2; counts[3] = n_reproj; }
+  return 0;
+}
+// flagOutlierByExclusionDist, rig_calibrator.cc:1003-1038
+int oracle_flag_exclusion(void* h, const double* image_size, const double* crop_size, uint8_t* inlier) {
+  Problem* P = (Problem*)h;
+  for (int64_t q = 0; q < P->nobs; q++) {
+    const int t = P->cam_sensor[P->ocid[q]];
+    if (std::abs((double)P->opix[2 * q] - image_size[2 * t] / 2.0) > crop_size[2 * t] / 2.0 ||
+        std::abs((double)P->opix[2 * q + 1] - image_size[2 * t + 1] / 2.0) > crop_size[2 * t + 1] / 2.0)
+      inlier[q] = 0;
+  }
+  return 0;
+}
+// UndistortCentered of one DISTORTED pixel, exported for the golden-vector tests (cv2.undistortPoints).
+void oracle_undistort(double w, double hgt, int nd, double f, const double* c, const double* dist, const double* pix, double* out) {
+  oracle::SensorConst s{{w / 2, hgt / 2}, nd}; double dummy = 0;
+  const double dc[2] = {pix[0] - w / 2, pix[1] - hgt / 2};
+  oracle::undistort_centered(s, f, c, nd > 0 ? dist : &dummy, dc, out);
 }
 }

@@ -29,7 +29,7 @@ CASES = {
 
 # Cases whose later iterations have rejected steps with 40-70 CG iterations: the Q-based CG stopping test then flips
 # on round-off, after which the two runs are on different (equally valid) paths.  They are compared on the common path.
-ITERS = {"depth_mesh": 5, "rig3_ragged_intr": 4}
+ITERS = {"depth_mesh": 5, "rig3_ragged_intr": 4, "offsets": 8}  # offsets: iteration 9 takes 24 CG steps along the weak time-offset direction
 
 
 def _run(lib, prefix, pr, snap, iters, **kw):
