@@ -180,6 +180,30 @@ class Binding:
                                                        _p(r, c_double_p), _p(J, c_double_p)))
         return r, J
 
+    # -- per-track steps around a pass (N1, N2) ------------------------------------------
+    def triangulate(self, inlier=None, xyz0=None):
+        """multiViewTriangulation at the current parameters: returns (xyz[P,3], inlier[N])."""
+        pr = self.pr
+        inl = np.ones(pr.num_obs, np.uint8) if inlier is None else np.ascontiguousarray(inlier, np.uint8).copy()
+        xyz = np.zeros(3 * pr.num_landmarks) if xyz0 is None else np.ascontiguousarray(xyz0, np.float64).ravel().copy()
+        self._ck(self._f("triangulate")(self.h, _p(inl, c_u8_p), _p(xyz, c_double_p)))
+        return xyz.reshape(-1, 3), inl
+
+    def flag_outliers(self, min_triangulation_angle, max_reprojection_error, inlier=None):
+        """flagOutliersByTriAngleAndReprojErr at the current parameters: returns (inlier[N], counts[4])."""
+        inl = np.ones(self.pr.num_obs, np.uint8) if inlier is None else np.ascontiguousarray(inlier, np.uint8).copy()
+        counts = np.zeros(4, np.int64)
+        self._ck(self._f("flag_outliers")(self.h, C.c_double(min_triangulation_angle), C.c_double(max_reprojection_error),
+                                          _p(inl, c_u8_p), _p(counts, c_i64_p)))
+        return inl, counts
+
+    def flag_exclusion(self, image_size, crop_size, inlier=None):
+        """flagOutlierByExclusionDist: image_size / crop_size are [T,2]."""
+        inl = np.ones(self.pr.num_obs, np.uint8) if inlier is None else np.ascontiguousarray(inlier, np.uint8).copy()
+        a = np.ascontiguousarray(image_size, np.float64).ravel(); b = np.ascontiguousarray(crop_size, np.float64).ravel()
+        self._ck(self._f("flag_exclusion")(self.h, _p(a, c_double_p), _p(b, c_double_p), _p(inl, c_u8_p)))
+        return inl
+
     def solve(self, options: SolveOptions | None = None, max_log=256, jac_mode=1, num_threads=0):
         o = options or default_options()
         s = Summary()

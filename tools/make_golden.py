@@ -109,8 +109,46 @@ def cauchy_and_lm_rules():
     sq = np.array([float(mp.sqrt(1 / (1 + mp.mpf(x) / mp.mpf(a) ** 2))) for x in s])
     np.savez(os.path.join(OUT, "cauchy.npz"), s=s, a=a, rho=rho, sqrt_rho1=sq)
 
+def undistortion():
+    """Convert<DISTORTED, UNDISTORTED_C> (camera_params.cc:316-355): radtan through cv2.undistortPoints (the call the
+    reference makes), FOV in closed form with mpmath, RPC through the second half of the coefficient block.
+    Own generator so that the older fixtures stay byte-identical."""
+    r2 = np.random.default_rng(20261104)
+    n = 200
+    f, c, wh = 608.0, np.array([640.5, 480.2]), np.array([1280.0, 960.0])
+    pix = np.stack([r2.uniform(40, 1240, n), r2.uniform(30, 930, n)], axis=1)
+    pix[0] = c                       # the optical centre itself (rd = 0 branch of the FOV model)
+    pix[1] = c + [3e-3, -2e-3]       # rd <= 1e-5
+    K = np.array([[f, 0, c[0]], [0, f, c[1]], [0, 0, 1.0]])
+    Pn = np.array([[f, 0, 0.0], [0, f, 0.0], [0, 0, 1.0]])   # undistorted intrinsics minus the undistorted half size
+    d4 = np.array([-0.25, 0.08, 0.0012, -0.0008]); d5 = np.array([0.06, -0.11, 0.0005, 0.0007, 0.02])
+    src = pix.reshape(-1, 1, 2).astype(np.float64)
+    rad4 = cv2.undistortPoints(src, K, np.array([d4[0], d4[1], d4[2], d4[3], 0.0]), None, Pn).reshape(n, 2)
+    rad5 = cv2.undistortPoints(src, K, d5, None, Pn).reshape(n, 2)
+    fov_w = 0.998
+    fov = np.zeros((n, 2))
+    for i in range(n):
+        nx, ny = (mp.mpf(pix[i, 0]) - mp.mpf(c[0])) / f, (mp.mpf(pix[i, 1]) - mp.mpf(c[1])) / f
+        rd = mp.sqrt(nx * nx + ny * ny)
+        conv = mp.mpf(1)
+        if rd > mp.mpf("1e-5"):
+            conv = mp.tan(rd * mp.mpf(fov_w)) / (2 * mp.tan(mp.mpf(fov_w) / 2)) / rd
+        fov[i] = [float(conv * nx * f), float(conv * ny * f)]
+    deg = 2
+    nco = 2 * (deg + 1) * (deg + 2) - 2
+    L = (deg + 1) * (deg + 2) // 2
+    und = np.zeros(nco)
+    und[1] = 1.0; und[L + (L - 1) + 2] = 1.0
+    und += r2.normal(0, 1, nco) * np.where(np.arange(nco) % 5 == 0, 1e-7, 1e-9)
+    dis = r2.normal(size=nco)        # first half: must not influence the undistortion
+    rpc = np.array([rpc_mp(pix[i] - wh / 2, und, deg) for i in range(n)])
+    np.savez(os.path.join(OUT, "undistort.npz"), pix=pix, focal=f, center=c, size=wh, none=pix - c, fov_w=fov_w, fov=fov,
+             radtan4_coeffs=d4, radtan4=rad4, radtan5_coeffs=d5, radtan5=rad5, rpc2_coeffs=np.concatenate([dis, und]), rpc2=rpc)
+
 
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
-    pose_interp(); distortion(); cauchy_and_lm_rules()
+    if len(sys.argv) > 1 and sys.argv[1] == "undistort":
+        undistortion(); print("wrote undistort.npz"); sys.exit(0)
+    pose_interp(); distortion(); cauchy_and_lm_rules(); undistortion()
     print("wrote", sorted(os.listdir(OUT)))
