@@ -4,6 +4,7 @@
 #pragma once
 #include "kernels_build.cuh"
 #include "kernels_eval.cuh"
+#include <cooperative_groups.h>
 
 namespace mvba {
 
@@ -112,11 +113,10 @@ __global__ void __launch_bounds__(256) precond_border_kernel(Reduced S, int use_
 // --- S x ----------------------------------------------------------------------------------
 // One warp per pose block row (lanes over the row's blocks), then warps for the border rows.
 // y must have its border part zeroed before the launch (pose rows add S_pb' x_pose atomically).
-__global__ void __launch_bounds__(256) spmv_kernel(Reduced S, Bsr A, const double* __restrict__ x, double* __restrict__ y,
-                                                    const int* __restrict__ done) {
-  if (done && *done) return;
-  const int lane = threadIdx.x & 31;
-  const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+// Row w of S x for one warp (w < nb: pose block row, else border row w - nb).
+// (x and y are deliberately not __restrict__: the fused PCG kernel reads vectors written earlier in the same launch,
+// which must not go through the non-coherent read-only path.)
+__device__ __forceinline__ void spmv_row(const Reduced& S, const Bsr& A, const double* x, double* y, int w, int lane) {
   const int B = S.B;
   if (w < A.nb) {
     double acc[7] = {0, 0, 0, 0, 0, 0, 0};
@@ -164,6 +164,14 @@ __global__ void __launch_bounds__(256) spmv_kernel(Reduced S, Bsr A, const doubl
     t = warp_sum(t);
     if (lane == 0) atomicAdd(y + S.npc + b, t);
   }
+}
+
+__global__ void __launch_bounds__(256) spmv_kernel(Reduced S, Bsr A, const double* __restrict__ x, double* __restrict__ y,
+                                                    const int* __restrict__ done) {
+  if (done && *done) return;
+  const int lane = threadIdx.x & 31;
+  const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (w < A.nb + S.B) spmv_row(S, A, x, y, w, lane);
 }
 
 // --- PCG steps ------------------------------------------------------------------------------
@@ -262,6 +270,103 @@ __global__ void pcg_check_kernel(PcgScal sc, int it, int refreshed, double eta, 
   *sc.iters = it;
   if (zeta < eta && it >= min_it) *sc.done = 1;
   else if (it >= max_it) *sc.done = 4;
+}
+
+// --- the whole PCG solve in ONE cooperative launch -------------------------------------------
+// Same arithmetic and stopping rules as the step kernels above (they remain as the fallback when the device cannot
+// co-schedule the grid), with grid-wide barriers instead of kernel boundaries: five per iteration
+//   z = M^-1 r, rho | p = z + beta p | q = S p | p.q | x, r, Q   (the Q test is evaluated at the top of the next iteration)
+// and no host round trip until the solve is over.  The reduced system (a few MB) stays L2 resident throughout.
+__device__ __forceinline__ void grid_accumulate(double v, double* out) { block_accumulate(v, out); }
+
+__global__ void __launch_bounds__(256) pcg_fused_kernel(Reduced S, Bsr A, const double* Mpp, const double* Mbb, const double* b, double* x,
+                                                         double* r, double* z, double* p, double* q, PcgScal sc, double eta, int min_it,
+                                                         int max_it) {
+  namespace cg = cooperative_groups;
+  cg::grid_group grid = cg::this_grid();
+  const int nf = S.nf, npc = S.npc, B = S.B;
+  const int gtid = blockIdx.x * blockDim.x + threadIdx.x, nthr = gridDim.x * blockDim.x;
+  const int lane = threadIdx.x & 31, gwarp = gtid >> 5, nwarp = nthr >> 5;
+  {
+    double v = 0;
+    for (int i = gtid; i < nf; i += nthr) { x[i] = 0; r[i] = b[i]; v += b[i] * b[i]; }
+    grid_accumulate(v, sc.bnorm2);
+  }
+  grid.sync();
+  int done = 0, it_done = 0;
+  double Q0 = 0.0;
+  for (int it = 1; it <= max_it; it++) {
+    {  // z = M^-1 r (block Jacobi), rho_it = r.z
+      double v = 0;
+      for (int g = gtid; g < nf; g += nthr) {
+        double s = 0;
+        if (g < npc) {
+          const int u = g / 7, k = g - 7 * u;
+          const double* M = Mpp + (size_t)u * 49 + 7 * k;
+          const double* rb = r + 7 * u;
+#pragma unroll
+          for (int j = 0; j < 7; j++) s += M[j] * rb[j];
+        } else {
+          const int bb = g - npc;
+          for (int j = 0; j < B; j++) s += Mbb[(size_t)bb * B + j] * r[npc + j];
+        }
+        z[g] = s;
+        v += s * r[g];
+      }
+      grid_accumulate(v, sc.it + 4 * it);
+    }
+    grid.sync();
+    if (it > 1) {  // Ceres' Q test of the previous iteration: zeta = it (Q1 - Q0) / Q1 < eta
+      const int pit = it - 1;
+      const double Q1 = sc.it[4 * pit + 2];
+      const double zeta = pit * (Q1 - Q0) / Q1;
+      Q0 = Q1;
+      it_done = pit;
+      if (zeta < eta && pit >= min_it) { done = 1; break; }
+    }
+    const double rho = sc.it[4 * it];
+    if (rho == 0.0 || !isfinite(rho)) { done = 2; break; }
+    const double beta = (it == 1) ? 0.0 : rho / sc.it[4 * (it - 1)];
+    for (int i = gtid; i < nf; i += nthr) { p[i] = z[i] + beta * p[i]; if (i >= npc) q[i] = 0; }
+    grid.sync();
+    for (int w = gwarp; w < A.nb + B; w += nwarp) spmv_row(S, A, p, q, w, lane);
+    grid.sync();
+    {
+      double v = 0;
+      for (int i = gtid; i < nf; i += nthr) v += p[i] * q[i];
+      grid_accumulate(v, sc.it + 4 * it + 1);
+    }
+    grid.sync();
+    const double pq = sc.it[4 * it + 1];
+    if (pq <= 0.0 || !isfinite(pq)) { done = 3; break; }  // "matrix is indefinite": keep the last iterate
+    const double alpha = rho / pq;
+    {
+      double v = 0;
+      for (int i = gtid; i < nf; i += nthr) {
+        const double xi = x[i] + alpha * p[i], ri = r[i] - alpha * q[i];
+        x[i] = xi; r[i] = ri;
+        v += -xi * (b[i] + ri);
+      }
+      if (it % 10 != 0) grid_accumulate(v, sc.it + 4 * it + 2);
+    }
+    if (it % 10 == 0) {  // residual_reset_period: r = b - S x, Q recomputed from it
+      for (int i = gtid; i < nf; i += nthr) if (i >= npc) q[i] = 0;
+      grid.sync();
+      for (int w = gwarp; w < A.nb + B; w += nwarp) spmv_row(S, A, x, q, w, lane);
+      grid.sync();
+      double v = 0;
+      for (int i = gtid; i < nf; i += nthr) { const double ri = b[i] - q[i]; r[i] = ri; v += -x[i] * (b[i] + ri); }
+      grid_accumulate(v, sc.it + 4 * it + 2);
+    }
+    grid.sync();  // r (read block-wise by the next preconditioner step) and Q are complete
+    if (it == max_it) {  // the last iteration's Q test
+      const double Q1 = sc.it[4 * it + 2];
+      const double zeta = it * (Q1 - Q0) / Q1;
+      it_done = it;
+      done = (zeta < eta && it >= min_it) ? 1 : 4;
+    }
+  }
+  if (gtid == 0) { *sc.done = done; *sc.iters = it_done; }
 }
 
 }  // namespace mvba

@@ -84,6 +84,7 @@ struct Solver {
   int* flags_host = nullptr;      // pinned
   size_t smem_build = 0, smem_backsub = 0;
   int wpb_build = 8, wpb_backsub = 8, grid_build = 1, grid_backsub = 1;
+  int pcg_coop_grid = 0;  // > 0: CTAs of the single-launch PCG (cooperative); 0: step kernels
   bool with_F = false;
   // pass A (camera-major F'F): block codes grouped by image, split into chunks
   DBuf<int32_t> citems, chunk_cam, chunk_beg;
@@ -396,6 +397,16 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
   MVBA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, build_kernel, 32 * s->wpb_build, s->smem_build));
   s->grid_build = std::max(1, std::min((v.P + s->wpb_build - 1) / s->wpb_build, h->sm_count * std::max(occ, 1)));
   s->grid_backsub = std::max(1, std::min((v.P + 127) / 128, h->sm_count * 16));
+  {  // single-launch PCG when the device can co-schedule the grid (MVBA_PCG_STEPS=1 forces the step kernels; developer switch)
+    int coop = 0, occ_pcg = 0;
+    MVBA_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, h->device));
+    MVBA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_pcg, pcg_fused_kernel, 256, 0));
+    const char* ev = std::getenv("MVBA_PCG_STEPS");
+    if (coop && occ_pcg > 0 && s->nf > 0 && !(ev && ev[0] == '1')) {
+      const int want = std::max((s->nb + s->B + 7) / 8, (s->nf + 255) / 256);
+      s->pcg_coop_grid = std::max(1, std::min(want, std::min(occ_pcg, 2) * h->sm_count));
+    }
+  }
   return MVBA_OK;
 }
 

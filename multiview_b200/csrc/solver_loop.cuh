@@ -96,6 +96,18 @@ inline int run_pcg(mvba_problem* h, const mvba_solve_options& o, int* iters_out)
   PcgScal sc{s->pcg_scal.p, s->pcg_flags.p, s->pcg_flags.p + 1, s->pcg_scal.p + (size_t)4 * (max_it + 2)};
   const int tb = 256, gb = (nf + tb - 1) / tb;
   const int spmv_warps = s->nb + s->B, spmv_grid = (spmv_warps * 32 + 255) / 256;
+  if (s->pcg_coop_grid > 0) {  // the whole solve in one cooperative launch, no host round trip
+    const double* Mpp = s->Mpp.p; const double* Mbb = s->Mbb.p; const double* bb = s->R.rhs;
+    double *xx = s->y.p, *rr = s->r.p, *zz = s->z.p, *pp = s->p.p, *qq = s->q.p;
+    double eta = o.eta; int min_it = o.min_linear_solver_iterations, mx = max_it;
+    void* args[] = {&s->R, &s->A, &Mpp, &Mbb, &bb, &xx, &rr, &zz, &pp, &qq, &sc, &eta, &min_it, &mx};
+    MVBA_CUDA(cudaLaunchCooperativeKernel((const void*)pcg_fused_kernel, dim3(s->pcg_coop_grid), dim3(256), args, 0, h->stream));
+    h->launches++;
+    MVBA_CUDA(cudaMemcpyAsync(s->flags_host, s->pcg_flags.p, 2 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    MVBA_CUDA(cudaStreamSynchronize(h->stream));
+    *iters_out = s->flags_host[1];
+    return MVBA_OK;
+  }
   pcg_init_kernel<<<gb, tb, 0, h->stream>>>(nf, s->npc, s->R.rhs, s->y.p, s->r.p, s->q.p, sc);
   h->launches++;
   const int batch = 8;
