@@ -67,12 +67,13 @@ static_assert(sizeof(TRec) == 200, "TRec layout");
 // DMMA fragment loads (8 rows x 4 consecutive doubles per half warp) bank-conflict free.
 __host__ __device__ inline int tile_kk(int K) { int kk = 3 * K; while ((kk & 15) != 4) kk++; return kk; }
 
-// Shared memory: Gt[L8max][KK] | Yt[L8max][KK] | ves[KK] | His[K][6] | cs[L8max] | Xs[icap][4 nx] | rec[icap]
+// Shared memory: Gt[L8max][KK] | Yt[L8max][KK] | ves[KK] | His[K][6] | cs[L8max] | Xs[2 icap][4 nx] | rec[2 icap]
+// (icap = residual blocks of ONE round; phase b1 evaluates two rounds at a time)
 // Gt[l][3 k + b] = row l of G = F'E of staged track k (dense in the window, zero where the track has no block),
 // Yt = G Hinv in the same layout: phase c is the GEMM  C += Yt Gt'  with the staged tracks as the K dimension.
 __host__ __device__ inline size_t tile_smem(int K, int icap, int nx, int L8max) {
   const size_t KK = tile_kk(K);
-  return (2 * (size_t)L8max * KK + KK + (size_t)K * 6 + (size_t)L8max + (size_t)icap * 4 * nx) * 8 + (size_t)icap * sizeof(TRec) + 16;
+  return (2 * (size_t)L8max * KK + KK + (size_t)K * 6 + (size_t)L8max + (size_t)2 * icap * 4 * nx) * 8 + (size_t)2 * icap * sizeof(TRec) + 16;
 }
 
 // Phase b1: one thread evaluates one residual block.  Nothing here is Jacobi-scaled on the f side (phase b2 scales
@@ -239,7 +240,7 @@ __global__ void __launch_bounds__(NT, 1) tile_kernel(View v, TileArgs a, Reduced
   double* His = ves + KK;
   double* cs = His + (size_t)K * 6;
   double* Xs = cs + a.L8max;
-  TRec* rec = reinterpret_cast<TRec*>(Xs + (size_t)a.icap * 4 * a.nx);
+  TRec* rec = reinterpret_cast<TRec*>(Xs + (size_t)2 * a.icap * 4 * a.nx);
   const int B = S.B;
   const int gid = lane >> 2, tig = lane & 3;
   double cost_acc = 0;
@@ -267,17 +268,23 @@ __global__ void __launch_bounds__(NT, 1) tile_kernel(View v, TileArgs a, Reduced
       cs[l] = (a.b.jscale_f && l < Lt) ? a.b.jscale_f[l < 7 * Wt ? 7 * w0 + l : S.npc + (l - 7 * Wt)] : 1.0;
 
     const int rd0 = a.tile_round0[t], rd1 = a.tile_round0[t + 1];
-    for (int rd = rd0; rd < rd1; rd++) {
-      const int trk0 = a.round_trk0[rd], kc = a.round_trk0[rd + 1] - trk0;
-      const int blk0 = a.round_blk0[rd], nit = a.round_blk0[rd + 1] - blk0;
-      const int grp0 = a.round_grp0[rd], ngrp = a.round_grp0[rd + 1] - grp0;
-      // ---- phase b1: one thread per residual block; everyone clears Gt ----
-      if (a.nx > 0) {
-        for (int q = tid; q < nit; q += NT)
-          cost_acc += tile_eval<true>(v, a.b, S, a.blk[blk0 + q], Wt, rec[q], Xs + (size_t)q * 4 * a.nx, jd);
-      } else {
-        for (int q = tid; q < nit; q += NT)
-          cost_acc += tile_eval<false>(v, a.b, S, a.blk[blk0 + q], Wt, rec[q], nullptr, nullptr);
+    for (int rd = rd0; rd < rd1; rd += 2) {
+      // ---- phase b1 for TWO rounds at once (one thread per residual block, so that most of the CTA evaluates);
+      //      the second round's records sit icap slots further.  Everyone clears Gt. ----
+      const int nsub = min(2, rd1 - rd);
+      {
+        const int blk0 = a.round_blk0[rd], nit0 = a.round_blk0[rd + 1] - blk0, nit = a.round_blk0[rd + nsub] - blk0;
+        if (a.nx > 0) {
+          for (int q = tid; q < nit; q += NT) {
+            const int slot = q < nit0 ? q : a.icap + (q - nit0);
+            cost_acc += tile_eval<true>(v, a.b, S, a.blk[blk0 + q], Wt, rec[slot], Xs + (size_t)slot * 4 * a.nx, jd);
+          }
+        } else {
+          for (int q = tid; q < nit; q += NT) {
+            const int slot = q < nit0 ? q : a.icap + (q - nit0);
+            cost_acc += tile_eval<false>(v, a.b, S, a.blk[blk0 + q], Wt, rec[slot], nullptr, nullptr);
+          }
+        }
       }
       {
         double2* gz = reinterpret_cast<double2*>(Gt);
@@ -287,6 +294,17 @@ __global__ void __launch_bounds__(NT, 1) tile_kernel(View v, TileArgs a, Reduced
       TPROF(0);
       __syncthreads();
       TPROF(1);
+      for (int sub = 0; sub < nsub; sub++) {
+      const int trk0 = a.round_trk0[rd + sub], kc = a.round_trk0[rd + sub + 1] - trk0;
+      const int grp0 = a.round_grp0[rd + sub], ngrp = a.round_grp0[rd + sub + 1] - grp0;
+      const TRec* rec_s = rec + (size_t)sub * a.icap;
+      const double* Xs_s = Xs + (size_t)sub * a.icap * 4 * a.nx;
+      if (sub > 0) {  // Gt of the first round was read by its phase c (behind that phase's closing barrier)
+        double2* gz = reinterpret_cast<double2*>(Gt);
+        const int nz = L8 * KK / 2;
+        for (int i = tid; i < nz; i += NT) gz[i] = make_double2(0.0, 0.0);
+        __syncthreads();
+      }
       // ---- phase b2: one thread per (group, row) gathers a row of G; threads k < kc reduce and invert E'E ----
       {
         const int4* gtab = reinterpret_cast<const int4*>(a.grp + grp0);
@@ -295,7 +313,7 @@ __global__ void __launch_bounds__(NT, 1) tile_kernel(View v, TileArgs a, Reduced
         while (i < 8 * ngrp) {
           const int inext = i + NT;
           const int4 rawn = inext < 8 * ngrp ? __ldg(gtab + (inext >> 3)) : make_int4(0, 0, 0, 0);
-          tile_gather(a, raw, i & 7, rec, cs, Gt, KK);
+          tile_gather(a, raw, i & 7, rec_s, cs, Gt, KK);
           raw = rawn; i = inext;
         }
       }
@@ -303,7 +321,7 @@ __global__ void __launch_bounds__(NT, 1) tile_kernel(View v, TileArgs a, Reduced
         const TTrk tk = a.ttrk[trk0 + tid];
         double H[6] = {0, 0, 0, 0, 0, 0}, gE[3] = {0, 0, 0};
         for (int i = 0; i < tk.n; i++) {
-          const TRec& r = rec[tk.q0 + i];
+          const TRec& r = rec_s[tk.q0 + i];
 #pragma unroll
           for (int k = 0; k < 6; k++) H[k] += r.H[k];
 #pragma unroll
@@ -327,8 +345,8 @@ __global__ void __launch_bounds__(NT, 1) tile_kernel(View v, TileArgs a, Reduced
           const TTrk tk = a.ttrk[trk0 + k];
           double* G = Gt + 3 * k;
           for (int i = 0; i < tk.n; i++) {
-            const int nxi = rec[tk.q0 + i].nx;
-            const double* X = Xs + (size_t)(tk.q0 + i) * 4 * a.nx;
+            const int nxi = rec_s[tk.q0 + i].nx;
+            const double* X = Xs_s + (size_t)(tk.q0 + i) * 4 * a.nx;
             for (int kk = lane; kk < nxi; kk += 32) {
               const int l2 = (int)X[4 * kk + 3];
               const double sc = cs[l2];
@@ -386,6 +404,7 @@ __global__ void __launch_bounds__(NT, 1) tile_kernel(View v, TileArgs a, Reduced
       TPROF(5);
       __syncthreads();
       TPROF(6);
+      }  // sub
     }
     // ---- flush: local column -> reduced column; window poses are consecutive pose blocks ----
     {

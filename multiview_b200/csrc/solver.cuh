@@ -280,7 +280,8 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
     for (int p = 0; p < v.P; p++) if (trk_any[p]) { if (W >= 0 && trk_span[p] <= W && trk_items[p] <= 32) order.push_back(p); else fb.push_back(p); }
     std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return trk_umin[a] < trk_umin[b]; });
     std::vector<int32_t> t0, tw0, twn;
-    const int tile_max = 512;
+    // at least ~6 tiles per CTA so that the static tile -> CTA assignment balances (small shards of a multi-GPU run)
+    const int tile_max = (int)std::max<size_t>(48, std::min<size_t>(512, order.size() / (size_t)(6 * std::max(h->sm_count, 1))));
     size_t i = 0;
     int wn_max = 0;
     while (i < order.size()) {
