@@ -1,0 +1,51 @@
+// camera_shim.cc -- C test shims over camera::CameraParameters (tests/test_camera_params.py).
+#include <string>
+
+#include "camera_params.h"
+
+static thread_local std::string g_cam_err;
+
+template <int S, int D> static void conv_all(const camera::CameraParameters& cp, int n, const double* in, double* out) {
+  for (int i = 0; i < n; i++) {
+    camera::Vector2d o;
+    cp.Convert<S, D>(camera::Vector2d(in[2 * i], in[2 * i + 1]), &o);
+    out[2 * i] = o[0]; out[2 * i + 1] = o[1];
+  }
+}
+
+extern "C" {
+const char* mvh_camera_last_error() { return g_cam_err.c_str(); }
+// frames: 0 RAW, 1 DISTORTED, 2 DISTORTED_C, 3 UNDISTORTED, 4 UNDISTORTED_C
+int mvh_camera_convert(const int* size, const double* focal, const double* center, const double* dist, int nd, const int* undist_size,
+                       const int* crop_offset, int src, int dst, int n, const double* in, double* out, double* k9, double* mean_focal) {
+  try {
+    using namespace camera;
+    CameraParameters cp(Vector2i(size[0], size[1]), Vector2d(focal[0], focal[1]), Vector2d(center[0], center[1]),
+                        std::vector<double>(dist, dist + nd));
+    if (undist_size) cp.SetUndistortedSize(Vector2i(undist_size[0], undist_size[1]));
+    if (crop_offset) cp.SetCropOffset(Vector2i(crop_offset[0], crop_offset[1]));
+    const int key = 10 * src + dst;
+    switch (key) {
+      case 10 * RAW + DISTORTED: conv_all<RAW, DISTORTED>(cp, n, in, out); break;
+      case 10 * DISTORTED + RAW: conv_all<DISTORTED, RAW>(cp, n, in, out); break;
+      case 10 * UNDISTORTED_C + DISTORTED_C: conv_all<UNDISTORTED_C, DISTORTED_C>(cp, n, in, out); break;
+      case 10 * DISTORTED_C + UNDISTORTED_C: conv_all<DISTORTED_C, UNDISTORTED_C>(cp, n, in, out); break;
+      case 10 * UNDISTORTED + UNDISTORTED_C: conv_all<UNDISTORTED, UNDISTORTED_C>(cp, n, in, out); break;
+      case 10 * UNDISTORTED_C + UNDISTORTED: conv_all<UNDISTORTED_C, UNDISTORTED>(cp, n, in, out); break;
+      case 10 * DISTORTED + UNDISTORTED: conv_all<DISTORTED, UNDISTORTED>(cp, n, in, out); break;
+      case 10 * UNDISTORTED + DISTORTED: conv_all<UNDISTORTED, DISTORTED>(cp, n, in, out); break;
+      case 10 * DISTORTED + UNDISTORTED_C: conv_all<DISTORTED, UNDISTORTED_C>(cp, n, in, out); break;
+      case 10 * UNDISTORTED_C + DISTORTED: conv_all<UNDISTORTED_C, DISTORTED>(cp, n, in, out); break;
+      default: throw std::runtime_error("Please use the explicitly specified conversions by using the correct enum.");
+    }
+    if (k9) {
+      Matrix3d k = src == RAW ? cp.GetIntrinsicMatrix<RAW>() : src == DISTORTED ? cp.GetIntrinsicMatrix<DISTORTED>()
+                 : src == DISTORTED_C ? cp.GetIntrinsicMatrix<DISTORTED_C>() : src == UNDISTORTED ? cp.GetIntrinsicMatrix<UNDISTORTED>()
+                 : cp.GetIntrinsicMatrix<UNDISTORTED_C>();
+      for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) k9[3 * r + c] = k(r, c);
+    }
+    if (mean_focal) *mean_focal = cp.GetFocalLength();
+    return 0;
+  } catch (const std::exception& e) { g_cam_err = e.what(); return -1; }
+}
+}

@@ -1,0 +1,94 @@
+"""camera::CameraParameters mirror (multiview_b200/host/camera_params.h) against the committed golden vectors:
+UNDISTORTED_C -> DISTORTED from tests/golden/distortion.npz (mpmath, cv2.projectPoints) and DISTORTED -> UNDISTORTED_C
+from tests/golden/undistort.npz (cv2.undistortPoints, mpmath), plus the frame algebra of the ten declared conversions and
+the five intrinsic matrices (camera_params.cc:374-451)."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = os.path.join(ROOT, "tests", "golden")
+RAW, DISTORTED, DISTORTED_C, UNDISTORTED, UNDISTORTED_C = range(5)
+dp, ip = C.POINTER(C.c_double), C.POINTER(C.c_int)
+
+
+@pytest.fixture(scope="module")
+def host():
+    path = os.path.join(ROOT, "multiview_b200", "libmvba_host.so")
+    subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "multiview_b200", "host")])
+    lib = C.CDLL(path)
+    lib.mvh_camera_last_error.restype = C.c_char_p
+    return lib
+
+
+def convert(lib, size, focal, center, dist, src, dst, pts, undist_size=None, crop=None, want_k=False):
+    size = np.asarray(size, np.int32); focal = np.asarray(focal, np.float64) * np.ones(2); center = np.asarray(center, np.float64)
+    dist = np.asarray(dist, np.float64); pts = np.ascontiguousarray(pts, np.float64); out = np.zeros_like(pts)
+    us = None if undist_size is None else np.asarray(undist_size, np.int32); cr = None if crop is None else np.asarray(crop, np.int32)
+    k = np.zeros(9); mf = C.c_double()
+    rc = lib.mvh_camera_convert(size.ctypes.data_as(ip), focal.ctypes.data_as(dp), center.ctypes.data_as(dp),
+                                dist.ctypes.data_as(dp) if dist.size else None, int(dist.size),
+                                None if us is None else us.ctypes.data_as(ip), None if cr is None else cr.ctypes.data_as(ip),
+                                src, dst, len(pts), pts.ctypes.data_as(dp), out.ctypes.data_as(dp), k.ctypes.data_as(dp), C.byref(mf))
+    if rc != 0:
+        raise RuntimeError(lib.mvh_camera_last_error().decode())
+    return (out, k.reshape(3, 3), mf.value) if want_k else out
+
+
+@pytest.mark.parametrize("model", ["none", "fov", "radtan4", "radtan5", "rpc2", "rpc3"])
+def test_distortion_direction(host, model):
+    g = np.load(os.path.join(GOLD, "distortion.npz"))
+    f, c, size, u = float(g["focal"]), g["center"], g["size"].astype(int), g["u"]
+    dist = {"none": [], "fov": [float(g["fov_w"])]}.get(model, None)
+    if dist is None:
+        dist = g[model + "_coeffs"]
+    got = convert(host, size, f, c, dist, UNDISTORTED_C, DISTORTED, u)
+    assert np.abs(got - g[model]).max() <= 1e-9 * max(1.0, np.abs(g[model]).max())
+
+
+@pytest.mark.parametrize("model", ["none", "fov", "radtan4", "radtan5", "rpc2"])
+def test_undistortion_direction(host, model):
+    g = np.load(os.path.join(GOLD, "undistort.npz"))
+    f, c, size, pix = float(g["focal"]), g["center"], g["size"].astype(int), g["pix"]
+    dist = {"none": [], "fov": [float(g["fov_w"])]}.get(model, None)
+    if dist is None:
+        dist = g[model + "_coeffs"]
+    got = convert(host, size, f, c, dist, DISTORTED, UNDISTORTED_C, pix)
+    assert np.abs(got - g[model]).max() <= 1e-9 * max(1.0, np.abs(g[model]).max())
+
+
+def test_frame_algebra_and_intrinsics(host):
+    rng = np.random.default_rng(4)
+    size, usize, crop = (1280, 960), (1500, 1200), (16, 8)
+    focal, center, dist = (608.0, 610.5), (640.5, 480.2), [0.998]
+    pts = rng.uniform(100, 900, (50, 2))
+    kw = dict(undist_size=usize, crop=crop)
+    a = convert(host, size, focal, center, dist, RAW, DISTORTED, pts, **kw)
+    assert np.allclose(a, pts - crop, rtol=0, atol=0)
+    assert np.allclose(convert(host, size, focal, center, dist, DISTORTED, RAW, a, **kw), pts, rtol=0, atol=1e-12)
+    uc = convert(host, size, focal, center, dist, DISTORTED, UNDISTORTED_C, pts, **kw)
+    u = convert(host, size, focal, center, dist, DISTORTED, UNDISTORTED, pts, **kw)
+    assert np.abs(u - (uc + np.array(usize) / 2.0)).max() <= 1e-12
+    assert np.abs(convert(host, size, focal, center, dist, UNDISTORTED, UNDISTORTED_C, u, **kw) - uc).max() <= 1e-10
+    assert np.abs(convert(host, size, focal, center, dist, UNDISTORTED_C, UNDISTORTED, uc, **kw) - u).max() <= 1e-10
+    dc = convert(host, size, focal, center, dist, UNDISTORTED_C, DISTORTED_C, uc, **kw)
+    assert np.abs(dc + np.array(size) / 2.0 - pts).max() <= 1e-8            # FOV model: distort(undistort(p)) = p
+    assert np.abs(convert(host, size, focal, center, dist, UNDISTORTED, DISTORTED, u, **kw) - pts).max() <= 1e-8
+    assert np.abs(convert(host, size, focal, center, dist, DISTORTED_C, UNDISTORTED_C, pts - np.array(size) / 2.0, **kw) - uc).max() <= 1e-10
+    want_c = {RAW: np.array(center) + crop, DISTORTED: np.array(center), DISTORTED_C: np.array(center) - np.array(size) / 2.0,
+              UNDISTORTED: np.array(usize) / 2.0, UNDISTORTED_C: np.zeros(2)}
+    pairs = {RAW: DISTORTED, DISTORTED: RAW, DISTORTED_C: UNDISTORTED_C, UNDISTORTED: UNDISTORTED_C, UNDISTORTED_C: UNDISTORTED}
+    for frame, dst in pairs.items():
+        _, k, mf = convert(host, size, focal, center, dist, frame, dst, pts[:1], want_k=True, **kw)
+        assert mf == (focal[0] + focal[1]) / 2.0                                 # GetFocalLength() is the mean of fx, fy
+        assert np.allclose(k, [[focal[0], 0, want_c[frame][0]], [0, focal[1], want_c[frame][1]], [0, 0, 1]], rtol=0, atol=1e-12)
+
+
+def test_undeclared_conversion_and_bad_distortion_length_are_errors(host):
+    with pytest.raises(RuntimeError, match="explicitly specified conversions"):
+        convert(host, (640, 480), 600.0, (320, 240), [], RAW, UNDISTORTED, np.zeros((1, 2)))
+    with pytest.raises(RuntimeError, match="irregular distortion vector size"):
+        convert(host, (640, 480), 600.0, (320, 240), [0.1, 0.2, 0.3], UNDISTORTED_C, DISTORTED, np.zeros((1, 2)))
