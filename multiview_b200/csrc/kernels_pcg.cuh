@@ -274,47 +274,129 @@ __global__ void pcg_check_kernel(PcgScal sc, int it, int refreshed, double eta, 
 
 // --- the whole PCG solve in ONE cooperative launch -------------------------------------------
 // Same arithmetic and stopping rules as the step kernels above (they remain as the fallback when the device cannot
-// co-schedule the grid), with grid-wide barriers instead of kernel boundaries: five per iteration
-//   z = M^-1 r, rho | p = z + beta p | q = S p | p.q | x, r, Q   (the Q test is evaluated at the top of the next iteration)
-// and no host round trip until the solve is over.  The reduced system (a few MB) stays L2 resident throughout.
-__device__ __forceinline__ void grid_accumulate(double v, double* out) { block_accumulate(v, out); }
+// co-schedule the grid), with grid-wide barriers instead of kernel boundaries and no host round trip until the solve is
+// over.  THREE barriers per iteration:
+//   P  per parameter block (8 lanes per pose block, one warp for the border): x += alpha p, r -= alpha q of the PREVIOUS
+//      iteration, its Q, then z = M^-1 r (block local) and rho = r.z                                   | barrier
+//      Ceres' Q test of the previous iteration, beta;  p = z + beta p                                  | barrier
+//   S  q = S p fused with p.q (the border rows of q are completed with atomics, so their share of p.q is taken from the
+//      terms as they are produced: p_b' (S_pb' p_u) per pose row, p_b (S_bb p_b)_b per border row)       | barrier
+// The reduced system (a few MB) stays L2 resident throughout.
+
+// Row w of S x as spmv_row, returning this lane's share of x'(S x).
+__device__ __forceinline__ double spmv_row_dot(const Reduced& S, const Bsr& A, const double* x, double* y, int w, int lane) {
+  const int B = S.B;
+  double dot = 0;
+  if (w < A.nb) {
+    double acc[7] = {0, 0, 0, 0, 0, 0, 0};
+    for (int e = A.row_ptr[w] + lane; e < A.row_ptr[w + 1]; e += 32) {
+      const int c = A.col[e], sl = A.slot[e];
+      const double* xb = x + 7 * c;
+      double xv[7];
+#pragma unroll
+      for (int k = 0; k < 7; k++) xv[k] = xb[k];
+      if (sl >= 0) {
+        const double* M = S.Spp + (size_t)sl * 49;
+#pragma unroll
+        for (int r = 0; r < 7; r++)
+#pragma unroll
+          for (int k = 0; k < 7; k++) acc[r] += M[7 * r + k] * xv[k];
+      } else {
+        const double* M = S.Spp + (size_t)(-sl - 1) * 49;
+#pragma unroll
+        for (int k = 0; k < 7; k++)
+#pragma unroll
+          for (int r = 0; r < 7; r++) acc[r] += M[7 * k + r] * xv[k];
+      }
+    }
+    double xr[7];
+#pragma unroll
+    for (int r = 0; r < 7; r++) xr[r] = x[7 * w + r];
+    for (int b = lane; b < B; b += 32) {
+      const double xb = x[S.npc + b];
+      double t = 0;
+#pragma unroll
+      for (int r = 0; r < 7; r++) { const double s = S.Spb[(size_t)(7 * w + r) * B + b]; acc[r] += s * xb; t += s * xr[r]; }
+      atomicAdd(y + S.npc + b, t);
+      dot += xb * t;                      // x_b (S_pb' x_u)_b
+    }
+#pragma unroll
+    for (int r = 0; r < 7; r++) acc[r] = warp_sum(acc[r]);
+    if (lane == 0) {
+#pragma unroll
+      for (int r = 0; r < 7; r++) { y[7 * w + r] = acc[r]; dot += xr[r] * acc[r]; }
+    }
+  } else {
+    const int b = w - A.nb;
+    if (b < B) {
+      double t = 0;
+      for (int c = lane; c < B; c += 32) t += S.Sbb[(size_t)b * B + c] * x[S.npc + c];
+      t = warp_sum(t);
+      if (lane == 0) { atomicAdd(y + S.npc + b, t); dot += x[S.npc + b] * t; }
+    }
+  }
+  return dot;
+}
 
 __global__ void __launch_bounds__(256) pcg_fused_kernel(Reduced S, Bsr A, const double* Mpp, const double* Mbb, const double* b, double* x,
                                                          double* r, double* z, double* p, double* q, PcgScal sc, double eta, int min_it,
                                                          int max_it) {
   namespace cg = cooperative_groups;
   cg::grid_group grid = cg::this_grid();
-  const int nf = S.nf, npc = S.npc, B = S.B;
+  const int nf = S.nf, npc = S.npc, B = S.B, nb = S.nb;
   const int gtid = blockIdx.x * blockDim.x + threadIdx.x, nthr = gridDim.x * blockDim.x;
   const int lane = threadIdx.x & 31, gwarp = gtid >> 5, nwarp = nthr >> 5;
-  {
-    double v = 0;
-    for (int i = gtid; i < nf; i += nthr) { x[i] = 0; r[i] = b[i]; v += b[i] * b[i]; }
-    grid_accumulate(v, sc.bnorm2);
-  }
+  const int sub = lane & 7, gbase = lane & ~7;
+  for (int i = gtid; i < nf; i += nthr) { x[i] = 0; r[i] = b[i]; }
   grid.sync();
   int done = 0, it_done = 0;
-  double Q0 = 0.0;
-  for (int it = 1; it <= max_it; it++) {
-    {  // z = M^-1 r (block Jacobi), rho_it = r.z
-      double v = 0;
-      for (int g = gtid; g < nf; g += nthr) {
-        double s = 0;
-        if (g < npc) {
-          const int u = g / 7, k = g - 7 * u;
-          const double* M = Mpp + (size_t)u * 49 + 7 * k;
-          const double* rb = r + 7 * u;
-#pragma unroll
-          for (int j = 0; j < 7; j++) s += M[j] * rb[j];
-        } else {
-          const int bb = g - npc;
-          for (int j = 0; j < B; j++) s += Mbb[(size_t)bb * B + j] * r[npc + j];
+  double Q0 = 0.0, alpha = 0.0;
+  bool pending = false;  // the x, r update of the previous iteration has not been applied yet
+  for (int it = 1; it <= max_it + 1; it++) {
+    // ---- P: pending update of iteration it - 1, its Q; z = M^-1 r and rho of iteration it ----
+    double vq = 0, vrho = 0;
+    for (int u0 = 4 * gwarp; u0 < nb; u0 += 4 * nwarp) {
+      const int u = u0 + (lane >> 3);
+      const bool act = u < nb && sub < 7;
+      const int i = act ? 7 * u + sub : 0;
+      double ri = 0;
+      if (act) {
+        ri = r[i];
+        if (pending) {
+          const double xi = x[i] + alpha * p[i];
+          ri -= alpha * q[i];
+          x[i] = xi; r[i] = ri;
+          vq += -xi * (b[i] + ri);
         }
-        z[g] = s;
-        v += s * r[g];
       }
-      grid_accumulate(v, sc.it + 4 * it);
+      double zi = 0;
+#pragma unroll
+      for (int j = 0; j < 7; j++) {
+        const double rj = __shfl_sync(0xffffffffu, ri, gbase + j);
+        if (act) zi += Mpp[(size_t)u * 49 + 7 * sub + j] * rj;
+      }
+      if (act) { z[i] = zi; vrho += zi * ri; }
     }
+    if (gwarp == nwarp - 1 && B > 0) {  // the border block: one warp
+      for (int bb = lane; bb < B; bb += 32) {
+        const int i = npc + bb;
+        if (pending) {
+          const double xi = x[i] + alpha * p[i], ri = r[i] - alpha * q[i];
+          x[i] = xi; r[i] = ri;
+          vq += -xi * (b[i] + ri);
+        }
+      }
+      __syncwarp();
+      for (int bb = lane; bb < B; bb += 32) {
+        double s = 0;
+        for (int j = 0; j < B; j++) s += Mbb[(size_t)bb * B + j] * r[npc + j];
+        z[npc + bb] = s;
+        vrho += s * r[npc + bb];
+      }
+    }
+    if (pending) block_accumulate(vq, sc.it + 4 * (it - 1) + 2);
+    if (it <= max_it) block_accumulate(vrho, sc.it + 4 * it);
+    pending = false;
     grid.sync();
     if (it > 1) {  // Ceres' Q test of the previous iteration: zeta = it (Q1 - Q0) / Q1 < eta
       const int pit = it - 1;
@@ -323,47 +405,34 @@ __global__ void __launch_bounds__(256) pcg_fused_kernel(Reduced S, Bsr A, const 
       Q0 = Q1;
       it_done = pit;
       if (zeta < eta && pit >= min_it) { done = 1; break; }
+      if (pit >= max_it) { done = 4; break; }
     }
     const double rho = sc.it[4 * it];
     if (rho == 0.0 || !isfinite(rho)) { done = 2; break; }
     const double beta = (it == 1) ? 0.0 : rho / sc.it[4 * (it - 1)];
     for (int i = gtid; i < nf; i += nthr) { p[i] = z[i] + beta * p[i]; if (i >= npc) q[i] = 0; }
     grid.sync();
-    for (int w = gwarp; w < A.nb + B; w += nwarp) spmv_row(S, A, p, q, w, lane);
-    grid.sync();
+    // ---- S: q = S p and p.q ----
     {
       double v = 0;
-      for (int i = gtid; i < nf; i += nthr) v += p[i] * q[i];
-      grid_accumulate(v, sc.it + 4 * it + 1);
+      for (int w = gwarp; w < nb + B; w += nwarp) v += spmv_row_dot(S, A, p, q, w, lane);
+      block_accumulate(v, sc.it + 4 * it + 1);
     }
     grid.sync();
     const double pq = sc.it[4 * it + 1];
     if (pq <= 0.0 || !isfinite(pq)) { done = 3; break; }  // "matrix is indefinite": keep the last iterate
-    const double alpha = rho / pq;
-    {
-      double v = 0;
-      for (int i = gtid; i < nf; i += nthr) {
-        const double xi = x[i] + alpha * p[i], ri = r[i] - alpha * q[i];
-        x[i] = xi; r[i] = ri;
-        v += -xi * (b[i] + ri);
-      }
-      if (it % 10 != 0) grid_accumulate(v, sc.it + 4 * it + 2);
-    }
-    if (it % 10 == 0) {  // residual_reset_period: r = b - S x, Q recomputed from it
-      for (int i = gtid; i < nf; i += nthr) if (i >= npc) q[i] = 0;
+    alpha = rho / pq;
+    pending = true;
+    if (it % 10 == 0) {  // residual_reset_period: x updated now, r = b - S x, Q recomputed from it
+      for (int i = gtid; i < nf; i += nthr) { x[i] += alpha * p[i]; if (i >= npc) q[i] = 0; }
       grid.sync();
-      for (int w = gwarp; w < A.nb + B; w += nwarp) spmv_row(S, A, x, q, w, lane);
+      for (int w = gwarp; w < nb + B; w += nwarp) spmv_row(S, A, x, q, w, lane);
       grid.sync();
       double v = 0;
       for (int i = gtid; i < nf; i += nthr) { const double ri = b[i] - q[i]; r[i] = ri; v += -x[i] * (b[i] + ri); }
-      grid_accumulate(v, sc.it + 4 * it + 2);
-    }
-    grid.sync();  // r (read block-wise by the next preconditioner step) and Q are complete
-    if (it == max_it) {  // the last iteration's Q test
-      const double Q1 = sc.it[4 * it + 2];
-      const double zeta = it * (Q1 - Q0) / Q1;
-      it_done = it;
-      done = (zeta < eta && it >= min_it) ? 1 : 4;
+      block_accumulate(v, sc.it + 4 * it + 2);
+      pending = false;
+      grid.sync();
     }
   }
   if (gtid == 0) { *sc.done = done; *sc.iters = it_done; }
