@@ -262,6 +262,27 @@ int mvba_flag_outliers(mvba_problem* h, double min_triangulation_angle, double m
  * (distorted_crop_size) of their sensor's image (image_size); both arrays hold 2 values per sensor. */
 int mvba_flag_exclusion(mvba_problem* h, const double* image_size, const double* crop_size, uint8_t* inlier);
 
+/* meshTriangulations / ray_mesh_intersect (rig_calibrator/src/texture_processing.cc:1436-1479, 1566-1625): the ray of
+ * every inlier feature (undistorted pixel, CURRENT camera) against a triangle mesh (float32 vertices, 3 indices per
+ * face; the reference's float32 triangle test of rayint/libs/acc/primitives.h), hits between min_ray_dist and
+ * max_ray_dist.  has_mesh[N] / mesh_xyz[3 N] receive the per-feature result (no hit: 0 and bad_xyz = (1e100, 1e100,
+ * 1e100), rig_calibrator.cc:1546) -- the arrays mvba_set_observations takes; pid_mesh_xyz[3 P] (may be NULL) the
+ * per-track mean of the hits or bad_xyz, the reference points of the MESH_TRI priors. */
+int mvba_mesh_intersect(mvba_problem* h, int64_t num_vertices, const float* vertices, int64_t num_faces,
+                        const uint32_t* faces, double min_ray_dist, double max_ray_dist, const uint8_t* inlier,
+                        uint8_t* has_mesh, double* mesh_xyz, double* pid_mesh_xyz);
+
+/* fitRpcDist / fitRpcUndist (camera_model/rpc_distortion.cc:619-728; fitCurrDegRPC :556-617; what
+ * CameraParameters::updateRpcUndistortion, camera_params.cc:214-254, and rig_calibrator/bin/fit_rpc.cc:80-146 run): fit an RPC
+ * model (ratio of polynomials of degree rpc_degree, 1..6, in x and y) mapping in_xy[2 n] to out_xy[2 n] in the least-squares
+ * sense, by degree continuation from the identity model, num_iterations Levenberg-Marquardt iterations per degree with
+ * Ceres' rules and tolerances (function / gradient 1e-16, parameter_tolerance given).  jacobian_mode 0 follows the
+ * reference's central-difference derivatives (closed form of the difference quotient), 1 uses exact derivatives.
+ * coeffs receives 2 (rpc_degree + 1)(rpc_degree + 2) - 2 values in the reference's packed order (num_x, den_x, num_y, den_y);
+ * stats (may be NULL): initial cost, final cost, LM iterations, successful steps.  Needs no problem handle. */
+int mvba_rpc_fit(int32_t device, int64_t n, const double* in_xy, const double* out_xy, int32_t rpc_degree,
+                 int32_t num_iterations, double parameter_tolerance, int32_t jacobian_mode, double* coeffs, double stats[4]);
+
 /* ---- measurement hooks (bench.py); device-resident inputs, CUDA-event timed ---- */
 /* Uploads parameters and keeps them resident. */
 int mvba_upload(mvba_problem* h);

@@ -204,6 +204,17 @@ class Binding:
         self._ck(self._f("flag_exclusion")(self.h, _p(a, c_double_p), _p(b, c_double_p), _p(inl, c_u8_p)))
         return inl
 
+    def mesh_intersect(self, vertices, faces, min_ray_dist, max_ray_dist, inlier=None):
+        """meshTriangulations at the current parameters: (has_mesh[N], mesh_xyz[N,3], pid_mesh_xyz[P,3])."""
+        pr = self.pr
+        inl = np.ones(pr.num_obs, np.uint8) if inlier is None else np.ascontiguousarray(inlier, np.uint8)
+        v = np.ascontiguousarray(vertices, np.float32); f = np.ascontiguousarray(faces, np.uint32)
+        has = np.zeros(pr.num_obs, np.uint8); xyz = np.zeros(3 * pr.num_obs); mean = np.zeros(3 * pr.num_landmarks)
+        self._ck(self._f("mesh_intersect")(self.h, C.c_int64(len(v)), _p(v, c_f32_p), C.c_int64(len(f)), f.ctypes.data_as(C.POINTER(C.c_uint32)),
+                                           C.c_double(min_ray_dist), C.c_double(max_ray_dist), _p(inl, c_u8_p), _p(has, c_u8_p),
+                                           _p(xyz, c_double_p), _p(mean, c_double_p)))
+        return has, xyz.reshape(-1, 3), mean.reshape(-1, 3)
+
     def solve(self, options: SolveOptions | None = None, max_log=256, jac_mode=1, num_threads=0):
         o = options or default_options()
         s = Summary()
@@ -235,3 +246,35 @@ def load_product():
 
 def bind_product(problem, device=0) -> Binding:
     return Binding(load_product(), "mvba_", problem, device)
+
+
+def rpc_num_params(deg: int) -> int:
+    return 2 * (deg + 1) * (deg + 2) - 2
+
+
+def rpc_fit(lib, prefix, in_xy, out_xy, deg, num_iterations=100, parameter_tolerance=1e-12, jacobian_mode=0, num_threads=0, device=0):
+    """fitRpcDist-style fit of out = rpc(in) through `mvba_rpc_fit` (product) or `oracle_rpc_fit` (checker):
+    (coeffs, {initial_cost, final_cost, iterations, successful})."""
+    a = np.ascontiguousarray(in_xy, np.float64); b = np.ascontiguousarray(out_xy, np.float64)
+    assert a.shape == b.shape and a.ndim == 2 and a.shape[1] == 2
+    c = np.zeros(rpc_num_params(deg)); st = np.zeros(4)
+    if prefix == "mvba_":
+        rc = lib.mvba_rpc_fit(C.c_int32(device), C.c_int64(len(a)), _p(a, c_double_p), _p(b, c_double_p), C.c_int32(deg), C.c_int32(num_iterations),
+                              C.c_double(parameter_tolerance), C.c_int32(jacobian_mode), _p(c, c_double_p), _p(st, c_double_p))
+        if rc != 0:
+            raise MvbaError(f"mvba_rpc_fit failed ({rc}): {lib.mvba_last_error().decode()}")
+    else:
+        rc = lib.oracle_rpc_fit(C.c_int64(len(a)), _p(a, c_double_p), _p(b, c_double_p), C.c_int32(deg), C.c_int32(num_iterations),
+                                C.c_double(parameter_tolerance), C.c_int32(num_threads), _p(c, c_double_p), _p(st, c_double_p))
+        if rc != 0:
+            raise MvbaError(f"oracle_rpc_fit failed ({rc})")
+    return c, dict(initial_cost=st[0], final_cost=st[1], iterations=int(st[2]), successful=int(st[3]))
+
+
+def compute_rpc(oracle_lib, pts, coeffs):
+    """compute_rpc (rpc_distortion.cc:116-160) of the oracle at an array of points."""
+    pts = np.ascontiguousarray(pts, np.float64); c = np.ascontiguousarray(coeffs, np.float64)
+    out = np.zeros_like(pts)
+    for i in range(len(pts)):
+        oracle_lib.oracle_compute_rpc(_p(pts[i], c_double_p), _p(c, c_double_p), C.c_int32(len(c)), _p(out[i], c_double_p))
+    return out

@@ -1,5 +1,7 @@
 // mvba.cu -- the C ABI of libmvba.so (include/mvba.h).  Single translation unit; all device code
 // is hand-written CUDA for sm_100a.  No CPU fallback and nothing from oracle/ is reachable here.
+#include <algorithm>
+#include <array>
 #include <chrono>
 #include <cstdlib>
 
@@ -7,6 +9,8 @@
 #include "setup.cuh"
 #include "solver.cuh"
 #include "kernels_tracks.cuh"
+#include "kernels_mesh.cuh"
+#include "rpc_fit.cuh"
 
 namespace mvba {
 thread_local std::string g_last_error;
@@ -326,11 +330,103 @@ int mvba_flag_exclusion(mvba_problem* h, const double* image_size, const double*
   return check_device_error(h);
 }
 
+// Median-split hierarchy over the triangles (host): nodes in depth-first order, triangles reordered leaf by leaf.
+static void build_bvh(const std::vector<mvba::MeshTri>& in, std::vector<mvba::BvhNode>& nodes, std::vector<mvba::MeshTri>& out) {
+  const int n = (int)in.size();
+  std::vector<int> idx(n);
+  for (int i = 0; i < n; i++) idx[i] = i;
+  std::vector<std::array<float, 3>> cen(n);
+  for (int i = 0; i < n; i++) for (int a = 0; a < 3; a++) cen[i][a] = (in[i].a[a] + in[i].b[a] + in[i].c[a]) / 3.0f;
+  struct Job { int node, first, last; };
+  std::vector<Job> todo;
+  nodes.clear(); out.clear();
+  nodes.push_back(mvba::BvhNode{});
+  todo.push_back({0, 0, n});
+  while (!todo.empty()) {
+    const Job j = todo.back(); todo.pop_back();
+    mvba::BvhNode nd{};
+    float clo[3], chi[3];
+    for (int a = 0; a < 3; a++) { nd.lo[a] = clo[a] = 3.4e38f; nd.hi[a] = chi[a] = -3.4e38f; }
+    for (int k = j.first; k < j.last; k++) {
+      const mvba::MeshTri& t = in[idx[k]];
+      for (int a = 0; a < 3; a++) {
+        nd.lo[a] = std::min(nd.lo[a], std::min(t.a[a], std::min(t.b[a], t.c[a])));
+        nd.hi[a] = std::max(nd.hi[a], std::max(t.a[a], std::max(t.b[a], t.c[a])));
+        clo[a] = std::min(clo[a], cen[idx[k]][a]); chi[a] = std::max(chi[a], cen[idx[k]][a]);
+      }
+    }
+    nd.left = nd.right = -1; nd.first = 0; nd.count = 0;
+    int axis = 0;
+    for (int a = 1; a < 3; a++) if (chi[a] - clo[a] > chi[axis] - clo[axis]) axis = a;
+    if (j.last - j.first <= 4 || !(chi[axis] > clo[axis])) {
+      nd.first = (int)out.size(); nd.count = j.last - j.first;
+      for (int k = j.first; k < j.last; k++) out.push_back(in[idx[k]]);
+    } else {
+      const int mid = (j.first + j.last) / 2;
+      std::nth_element(idx.begin() + j.first, idx.begin() + mid, idx.begin() + j.last, [&](int p, int q) { return cen[p][axis] < cen[q][axis]; });
+      nd.left = (int)nodes.size(); nodes.push_back(mvba::BvhNode{});
+      nd.right = (int)nodes.size(); nodes.push_back(mvba::BvhNode{});
+      todo.push_back({nd.left, j.first, mid});
+      todo.push_back({nd.right, mid, j.last});
+    }
+    nodes[j.node] = nd;
+  }
+}
+
+int mvba_mesh_intersect(mvba_problem* h, int64_t num_vertices, const float* vertices, int64_t num_faces, const uint32_t* faces,
+                        double min_ray_dist, double max_ray_dist, const uint8_t* inlier, uint8_t* has_mesh, double* mesh_xyz, double* pid_mesh_xyz) {
+  mvba::DBuf<uint8_t> d_in, d_has; mvba::DBuf<double> d_xyz, d_mean; mvba::DBuf<mvba::BvhNode> d_nodes; mvba::DBuf<mvba::MeshTri> d_tris;
+  int rc = tracks_begin(h, inlier, d_in); if (rc) return rc;
+  if (!vertices || !faces || num_faces < 1 || num_vertices < 3 || !has_mesh || !mesh_xyz) return fail(MVBA_EINVAL, "mvba_mesh_intersect: bad argument");
+  std::vector<mvba::MeshTri> tris((size_t)num_faces), sorted;
+  for (int64_t f = 0; f < num_faces; f++) {
+    for (int k = 0; k < 3; k++) if (faces[3 * f + k] >= (uint64_t)num_vertices) return fail(MVBA_EINVAL, "mvba_mesh_intersect: face index out of range");
+    for (int a = 0; a < 3; a++) {
+      tris[f].a[a] = vertices[3 * (size_t)faces[3 * f] + a]; tris[f].b[a] = vertices[3 * (size_t)faces[3 * f + 1] + a];
+      tris[f].c[a] = vertices[3 * (size_t)faces[3 * f + 2] + a];
+    }
+  }
+  std::vector<mvba::BvhNode> nodes;
+  build_bvh(tris, nodes, sorted);
+  MVBA_CUDA(d_nodes.upload(nodes)); MVBA_CUDA(d_tris.upload(sorted));
+  const View& v = h->view;
+  MVBA_CUDA(d_has.alloc((size_t)std::max<int64_t>(v.N, 1))); MVBA_CUDA(d_xyz.alloc((size_t)3 * std::max<int64_t>(v.N, 1)));
+  MVBA_CUDA(d_mean.alloc((size_t)3 * std::max(v.P, 1)));
+  if (v.N > 0) {
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((v.N + 127) / 128, (int64_t)h->sm_count * 16));
+    mesh_intersect_kernel<<<grid, 128, 0, h->stream>>>(v, h->d_x.p, h->d_tab.p, d_nodes.p, d_tris.p, min_ray_dist, max_ray_dist, d_in.p, d_has.p, d_xyz.p);
+    const int grid2 = std::max(1, std::min((v.P + 127) / 128, h->sm_count * 16));
+    mesh_track_mean_kernel<<<grid2, 128, 0, h->stream>>>(v, d_has.p, d_xyz.p, d_mean.p);
+    h->launches += 2;
+    MVBA_CUDA(cudaGetLastError());
+    MVBA_CUDA(cudaMemcpyAsync(has_mesh, d_has.p, (size_t)v.N, cudaMemcpyDeviceToHost, h->stream));
+    MVBA_CUDA(cudaMemcpyAsync(mesh_xyz, d_xyz.p, sizeof(double) * 3 * v.N, cudaMemcpyDeviceToHost, h->stream));
+    if (pid_mesh_xyz) MVBA_CUDA(cudaMemcpyAsync(pid_mesh_xyz, d_mean.p, sizeof(double) * 3 * v.P, cudaMemcpyDeviceToHost, h->stream));
+  }
+  return check_device_error(h);
+}
+
 int mvba_nccl_unique_id(uint8_t id128[128]) { return comm_unique_id(id128); }
 int mvba_comm_init(mvba_problem* h, int32_t rank, int32_t nranks, const uint8_t id128[128]) {
   if (!h) return fail(MVBA_EINVAL, "mvba_comm_init: null handle");
   int rc = ready(h); if (rc) return rc;
   return comm_init(h, rank, nranks, id128);
+}
+
+int mvba_rpc_fit(int32_t device, int64_t n, const double* in_xy, const double* out_xy, int32_t rpc_degree, int32_t num_iterations,
+                 double parameter_tolerance, int32_t jacobian_mode, double* coeffs, double stats[4]) {
+  if (n < 1 || !in_xy || !out_xy || !coeffs || rpc_degree < 1 || rpc_degree > mvba::RPC_MAX_DEG || num_iterations < 0)
+    return fail(MVBA_EINVAL, "mvba_rpc_fit: bad argument");
+  int rc = ensure_device(device); if (rc) return rc;
+  MVBA_CUDA(cudaSetDevice(device));
+  cudaDeviceProp p; MVBA_CUDA(cudaGetDeviceProperties(&p, device));
+  mvba::RpcFitter F;
+  rc = F.init(n, in_xy, out_xy, p.multiProcessorCount); if (rc) return rc;
+  std::vector<double> c; mvba::RpcFitStats st;
+  rc = mvba::rpc_fit_all(F, rpc_degree, num_iterations, parameter_tolerance, jacobian_mode, c, &st); if (rc) return rc;
+  for (size_t i = 0; i < c.size(); i++) coeffs[i] = c[i];
+  if (stats) { stats[0] = st.initial_cost; stats[1] = st.final_cost; stats[2] = st.iterations; stats[3] = st.successful; }
+  return MVBA_OK;
 }
 
 }  // extern "C"

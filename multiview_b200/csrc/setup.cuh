@@ -14,8 +14,12 @@ static inline int rpc_degree_of(int num_dist) {  // rpc_distortion.cc:43-45
   return (int)std::round(std::sqrt(2.0 * num_dist + 5.0) / 2.0 - 1.5);
 }
 
+int allreduce_flags(mvba_problem* h, std::vector<uint8_t>& flags);  // solver.cuh: element-wise OR across ranks
+void solver_destroy(mvba_problem* h);                                  // solver.cuh
+
 inline int setup(mvba_problem* h) {
   if (h->built) return MVBA_OK;
+  solver_destroy(h);  // structure tables of an earlier layout
   if (!h->have_params || !h->have_cams || !h->have_obs)
     return fail(MVBA_ESTATE, "mvba: set_params, set_cameras and set_observations must precede evaluation");
   const mvba_config& c = h->cfg;
@@ -112,6 +116,19 @@ inline int setup(mvba_problem* h) {
   h->nres = row; h->nblocks = blocks;
   v.n_dtri = (int64_t)h->h_dtri_obs.size(); v.n_dmesh = (int64_t)h->h_dmesh_obs.size();
   v.n_prior = n_pm + n_pt; v.n_pm = n_pm;
+
+  // Multi-rank: the column layout must be the same on every rank, so "used by at least one residual" means used on ANY rank
+  // (a landmark shard that never sees an image would otherwise drop that image's pose block and shift every later column).
+  if (h->nranks > 1) {
+    std::vector<uint8_t> flags;
+    flags.insert(flags.end(), pose_used.begin(), pose_used.end());
+    flags.insert(flags.end(), sens_used.begin(), sens_used.end());
+    flags.insert(flags.end(), sens_depth.begin(), sens_depth.end());
+    int rc = allreduce_flags(h, flags); if (rc) return rc;
+    std::copy(flags.begin(), flags.begin() + npose, pose_used.begin());
+    std::copy(flags.begin() + npose, flags.begin() + npose + T, sens_used.begin());
+    std::copy(flags.begin() + npose + T, flags.end(), sens_depth.begin());
+  }
 
   // ---- parameter vector layout ----
   int o = 0;

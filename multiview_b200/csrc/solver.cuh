@@ -55,6 +55,7 @@ inline int comm_init(mvba_problem* h, int rank, int nranks, const uint8_t* id128
   int rc = ((init_t)dlsym(n.lib, "ncclCommInitRank"))(&h->nccl_comm, nranks, id, rank);
   if (rc) return fail(MVBA_ENCCL, std::string("ncclCommInitRank: ") + n.GetErrorString(rc));
   h->rank = rank; h->nranks = nranks;
+  h->built = false;  // the column layout becomes the union over ranks (setup.cuh)
   return MVBA_OK;
 }
 // op: 0 sum, 2 max (ncclRedOp_t); dtype 8 = ncclFloat64, 5 = ncclUint64
@@ -63,6 +64,17 @@ inline int allreduce(mvba_problem* h, void* buf, size_t n, int dtype, int op) {
   Nccl& nc = nccl();
   int rc = nc.AllReduce(buf, buf, n, dtype, op, h->nccl_comm, h->stream);
   return rc ? fail(MVBA_ENCCL, std::string("ncclAllReduce: ") + nc.GetErrorString(rc)) : MVBA_OK;
+}
+
+// Element-wise OR of a byte table across ranks (ncclUint8 = 1, ncclMax = 2): layout decisions every rank must share.
+inline int allreduce_flags(mvba_problem* h, std::vector<uint8_t>& flags) {
+  if (h->nranks <= 1 || flags.empty()) return MVBA_OK;
+  DBuf<uint8_t> d;
+  MVBA_CUDA(d.upload(flags));
+  int rc = allreduce(h, d.p, flags.size(), 1, 2); if (rc) return rc;
+  MVBA_CUDA(cudaStreamSynchronize(h->stream));
+  MVBA_CUDA(cudaMemcpy(flags.data(), d.p, flags.size(), cudaMemcpyDeviceToHost));
+  return MVBA_OK;
 }
 
 struct Timers;
@@ -149,6 +161,7 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
     trk_any[p] = items > 0; trk_items[p] = items;
   }
   for (int u = 0; u < nb; u++) flag[(size_t)u * nb + u] = 1;  // diagonal always present (damping)
+  { int rc = allreduce_flags(h, flag); if (rc) return rc; }      // block pattern of S = union over the ranks' landmark shards
   std::vector<int32_t> pairtab((size_t)nb * nb, -1), row_ptr(nb + 1, 0), col, slot;
   int64_t ns = 0;
   std::vector<std::vector<std::pair<int, int>>> rows(nb);

@@ -189,35 +189,50 @@ class Problem:
         for k, v in self.param_arrays().items():
             v[...] = snap[k]
 
-    def shard(self, rank: int, world: int) -> "Problem":
-        """Landmark shard for rank `rank` of `world`: contiguous pid ranges balanced by observation
-        count; cameras and all non-landmark parameters are replicated."""
+    def shard(self, rank: int, world: int, locality: bool = True) -> "Problem":
+        """Landmark shard for rank `rank` of `world`: ranges of tracks balanced by observation count; cameras and all
+        non-landmark parameters are replicated.  With `locality` the tracks are first ordered by the
+        earliest image that sees them, so that a rank's tracks touch ~1/world of the images (pass A then works on long
+        per-image runs instead of `world` times shorter ones, and the rank's Schur blocks form one band)."""
         import copy
         P = self.num_landmarks
         counts = np.bincount(self.pid, minlength=P)
-        cum = np.concatenate([[0], np.cumsum(counts)])
+        start = np.concatenate([[0], np.cumsum(counts)])
+        if locality and P > 0:
+            first_cid = np.full(P, np.iinfo(np.int32).max, np.int64)
+            np.minimum.at(first_cid, self.pid, self.cid)
+            order = np.argsort(first_cid, kind="stable")
+        else:
+            order = np.arange(P)
+        cum = np.concatenate([[0], np.cumsum(counts[order])])
         total = cum[-1]
         bounds = [int(np.searchsorted(cum, total * r / world, side="left")) for r in range(world)] + [P]
         bounds[0] = 0
         lo, hi = bounds[rank], bounds[rank + 1]
-        o0, o1 = int(cum[lo]), int(cum[hi])
+        tracks = order[lo:hi]                                   # global pid of the shard's tracks, in shard order
+        n_t = counts[tracks]
+        # observation indices of the shard, track-major in shard order (cid ascending inside a track is preserved)
+        obs = (np.repeat(start[tracks], n_t) + (np.arange(int(n_t.sum())) - np.repeat(np.cumsum(n_t) - n_t, n_t))).astype(np.int64)
+        newpid = np.full(P, -1, np.int64); newpid[tracks] = np.arange(hi - lo)
         q = copy.copy(self)
-        q.xyz = self.xyz[3 * lo:3 * hi].copy()
-        q.pid = (self.pid[o0:o1] - lo).astype(np.int32)
-        q.cid = self.cid[o0:o1].copy()
-        q.pix = self.pix[2 * o0:2 * o1].copy()
+        q.xyz = self.xyz.reshape(-1, 3)[tracks].reshape(-1).copy()
+        q.pid = np.repeat(np.arange(hi - lo), n_t).astype(np.int32)
+        q.cid = self.cid[obs].copy()
+        q.pix = self.pix.reshape(-1, 2)[obs].reshape(-1).copy()
         for nm, w in (("has_depth", 1), ("depth_xyz", 3), ("has_mesh", 1), ("mesh_xyz", 3)):
             a = getattr(self, nm)
-            setattr(q, nm, None if a is None else a[w * o0:w * o1].copy())
+            setattr(q, nm, None if a is None else a.reshape(-1, w)[obs].reshape(-1).copy())
         q.priors = {}
         for kind, (ppid, ref, w, th) in self.priors.items():
-            sel = (ppid >= lo) & (ppid < hi)
-            q.priors[kind] = ((ppid[sel] - lo).astype(np.int32), ref.reshape(-1, 3)[sel].reshape(-1).copy(), w, th)
+            np_ = newpid[ppid]
+            sel = np.flatnonzero(np_ >= 0)
+            sel = sel[np.argsort(np_[sel], kind="stable")]      # priors follow the shard's track order
+            q.priors[kind] = (np_[sel].astype(np.int32), ref.reshape(-1, 3)[sel].reshape(-1).copy(), w, th)
         # replicated parameter blocks get their own copies so ranks do not alias in one process
         for nm in ("world_to_ref", "ref_to_cam", "offsets", "focal", "center", "distortion", "depth_to_image",
                    "depth_scale", "world_to_cam"):
             setattr(q, nm, getattr(self, nm).copy())
-        q.truth = dict(self.truth, pid_range=(lo, hi))
+        q.truth = dict(self.truth, pid_range=(lo, hi), tracks=tracks)
         return q
 
 

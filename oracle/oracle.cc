@@ -23,6 +23,7 @@
 #include "../include/mvba.h"
 #include "functors.h"
 #include "tracks.h"
+#include "rpc_fit.h"
 
 namespace oracle {
 
@@ -984,10 +985,58 @@ int oracle_flag_exclusion(void* h, const double* image_size, const double* crop_
   }
   return 0;
 }
+// meshTriangulations, texture_processing.cc:1566-1625
+int oracle_mesh_intersect(void* h, int64_t num_vertices, const float* vertices, int64_t num_faces, const uint32_t* faces, double min_ray_dist,
+                          double max_ray_dist, const uint8_t* inlier, uint8_t* has_mesh, double* mesh_xyz, double* pid_mesh_xyz) {
+  Problem* P = (Problem*)h; ensure(P);
+  auto cb = cam_blocks(*P);
+  const double bad = 1e100;
+  int64_t i = 0;
+  while (i < P->nobs) {
+    const int pid = P->opid[i];
+    int64_t j = i;
+    while (j < P->nobs && P->opid[j] == pid) j++;
+    double avg[3] = {0, 0, 0}; int n = 0;
+    for (int64_t q = i; q < j; q++) {
+      has_mesh[q] = 0;
+      for (int a = 0; a < 3; a++) mesh_xyz[3 * q + a] = bad;
+      if (!inlier[q]) continue;
+      const oracle::RBlock& b = *cb[q];
+      const oracle::SensorConst& s = P->sensors[b.sensor];
+      const double f = P->pbs[b.pb[5]].ptr[0];
+      double dummy = 0;
+      const double dc[2] = {b.meas[0] - s.half[0], b.meas[1] - s.half[1]};
+      double u[2], out[3];
+      oracle::undistort_centered(s, f, P->pbs[b.pb[6]].ptr, s.nd > 0 ? P->pbs[b.pb[7]].ptr : &dummy, dc, u);
+      if (oracle::ray_mesh_brute(u, f, block_world_to_cam(*P, b), vertices, faces, num_faces, min_ray_dist, max_ray_dist, out)) {
+        has_mesh[q] = 1;
+        for (int a = 0; a < 3; a++) { mesh_xyz[3 * q + a] = out[a]; avg[a] += out[a]; }
+        n++;
+      }
+    }
+    if (pid_mesh_xyz) for (int a = 0; a < 3; a++) pid_mesh_xyz[3 * (size_t)pid + a] = n >= 1 ? avg[a] / n : bad;
+    i = j;
+  }
+  return 0;
+}
 // UndistortCentered of one DISTORTED pixel, exported for the golden-vector tests (cv2.undistortPoints).
 void oracle_undistort(double w, double hgt, int nd, double f, const double* c, const double* dist, const double* pix, double* out) {
   oracle::SensorConst s{{w / 2, hgt / 2}, nd}; double dummy = 0;
   const double dc[2] = {pix[0] - w / 2, pix[1] - hgt / 2};
   oracle::undistort_centered(s, f, c, nd > 0 ? dist : &dummy, dc, out);
 }
+// fitRpcDist-style fit (rpc_fit.h): coeffs[2 (deg + 1)(deg + 2) - 2]; stats = {initial cost, final cost, iterations, successful steps}
+int oracle_rpc_fit(int64_t n, const double* in_xy, const double* out_xy, int32_t deg, int32_t num_iterations, double parameter_tolerance,
+                   int32_t num_threads, double* coeffs, double* stats) {
+  if (n <= 0 || deg < 1 || deg > 7) return -1;
+  int prev = omp_get_max_threads();
+  if (num_threads > 0) omp_set_num_threads(num_threads);
+  std::vector<double> c; oracle::RpcFitStats st{};
+  oracle::rpc_fit(n, in_xy, out_xy, deg, num_iterations, parameter_tolerance, c, &st);
+  omp_set_num_threads(prev);
+  for (size_t i = 0; i < c.size(); i++) coeffs[i] = c[i];
+  if (stats) { stats[0] = st.initial_cost; stats[1] = st.final_cost; stats[2] = st.iterations; stats[3] = st.successful; }
+  return 0;
+}
+void oracle_compute_rpc(const double* p, const double* coeffs, int32_t n, double* out) { oracle::compute_rpc(p, coeffs, n, out); }
 }

@@ -83,4 +83,54 @@ inline void triangulate_views(const std::vector<View34>& views, double X[3]) {
   }
 }
 
+// ---- ray / mesh (rayint/libs/acc/primitives.h:100-136, float32 exactly as written there; compiled with -ffp-contract=off) ----
+inline float dot3f(const float* a, const float* b) { float s = 0.0f; s = s + a[0] * b[0]; s = s + a[1] * b[1]; s = s + a[2] * b[2]; return s; }
+
+inline bool ray_tri(const float* o, const float* d, float tmin, float tmax, const float* A, const float* B, const float* C, float* t_out) {
+  float v0[3], v1[3], oa[3];
+  for (int i = 0; i < 3; i++) { v0[i] = B[i] - A[i]; v1[i] = C[i] - A[i]; oa[i] = o[i] - A[i]; }
+  float n[3] = {v1[1] * v0[2] - v1[2] * v0[1], v1[2] * v0[0] - v1[0] * v0[2], v1[0] * v0[1] - v1[1] * v0[0]};
+  float len = std::sqrt(dot3f(n, n));
+  if (len < std::numeric_limits<float>::epsilon()) return false;
+  for (int i = 0; i < 3; i++) n[i] = n[i] / len;
+  double cosine = dot3f(n, d);
+  if (std::abs(cosine) < std::numeric_limits<double>::epsilon()) return false;
+  float t = -dot3f(n, oa) / cosine;
+  if (t < tmin || tmax < t) return false;
+  float v2[3];
+  for (int i = 0; i < 3; i++) v2[i] = oa[i] + t * d[i];
+  float d00 = dot3f(v0, v0), d01 = dot3f(v0, v1), d11 = dot3f(v1, v1), d20 = dot3f(v2, v0), d21 = dot3f(v2, v1);
+  double denom = d00 * d11 - d01 * d01;
+  float b1 = (d11 * d20 - d01 * d21) / denom;
+  float b2 = (d00 * d21 - d01 * d20) / denom;
+  float b0 = 1.0f - b1 - b2;
+  *t_out = t;
+  const float eps = 1e-3;
+  return -eps <= b0 && b0 <= 1.0f + eps && -eps <= b1 && b1 <= 1.0f + eps && -eps <= b2 && b2 <= 1.0f + eps;
+}
+
+// ray_mesh_intersect (texture_processing.cc:1436-1479) without an acceleration structure: the nearest accepted hit over
+// ALL triangles, which is what the BVH traversal returns.
+inline bool ray_mesh_brute(const double u[2], double f, const Aff<double>& w2c, const float* verts, const uint32_t* faces, int64_t nfaces,
+                           double min_dist, double max_dist, double out[3]) {
+  double ray[3] = {u[0] / f, u[1] / f, 1.0};
+  double rn = std::sqrt(ray[0] * ray[0] + ray[1] * ray[1] + ray[2] * ray[2]);
+  for (int a = 0; a < 3; a++) ray[a] /= rn;
+  Aff<double> c2w = aff_inverse(w2c);
+  double wr[3], ctr[3] = {c2w.t[0], c2w.t[1], c2w.t[2]};
+  for (int a = 0; a < 3; a++) wr[a] = c2w.m[a][0] * ray[0] + c2w.m[a][1] * ray[1] + c2w.m[a][2] * ray[2];
+  float o[3] = {(float)ctr[0], (float)ctr[1], (float)ctr[2]}, d[3] = {(float)wr[0], (float)wr[1], (float)wr[2]};
+  float dn = std::sqrt(dot3f(d, d));
+  for (int a = 0; a < 3; a++) d[a] = d[a] / dn;
+  float tmin = (float)min_dist, tmax = (float)max_dist, best = std::numeric_limits<float>::infinity();
+  for (int64_t k = 0; k < nfaces; k++) {
+    float t;
+    if (ray_tri(o, d, tmin, tmax, verts + 3 * (size_t)faces[3 * k], verts + 3 * (size_t)faces[3 * k + 1], verts + 3 * (size_t)faces[3 * k + 2], &t) &&
+        !(t > best)) { best = t; tmax = t; }
+  }
+  if (!(best < std::numeric_limits<float>::infinity())) return false;
+  for (int a = 0; a < 3; a++) out[a] = ctr[a] + (double)best * wr[a];
+  return true;
+}
+
 }  // namespace oracle
