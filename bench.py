@@ -169,8 +169,9 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     lib = _abi.load_product()
     pr_full = synth.config(args.config, scale=args.scale)
-    # contiguous landmark ranges by default (measured at N = 2, 4, 8); MVBA_SHARD_LOCALITY=1 orders tracks by earliest image first
-    locality = os.environ.get("MVBA_SHARD_LOCALITY", "0") == "1"
+    # landmark ranges cut after ordering the tracks by the earliest image that sees them (each rank touches ~1/N of the images;
+    # measured at N = 2 and 8, profiles/r01d_scale_*); MVBA_SHARD_LOCALITY=0 cuts the ranges in input order instead
+    locality = os.environ.get("MVBA_SHARD_LOCALITY", "1") == "1"
     pr = pr_full.shard(rank, world, locality=locality) if world > 1 else pr_full
     g = _abi.Binding(lib, "mvba_", pr, device=local)
     if world > 1:
@@ -201,8 +202,12 @@ def run_ours(args):
     sampler.mark()
     t0 = time.perf_counter()
     s, log = g.solve(_abi.default_options(max_num_iterations=args.steps, **opts))
+    wall_solve = time.perf_counter() - t0
     barrier()
     wall = time.perf_counter() - t0
+    if os.environ.get("MVBA_BENCH_DEBUG"):
+        print(f"[rank {rank}] python wall around solve {wall_solve:.4f} s, with barrier {wall:.4f} s, mvba seconds_total {s.seconds_total:.4f}, "
+              f"seconds_device {s.seconds_device:.4f}", file=sys.stderr, flush=True)
     clocks = sampler.stop() if rank == 0 else None
     steps = s.num_iterations
     times = torch.tensor([s.seconds_device, wall, s.seconds_build_kernel, s.seconds_build, s.seconds_linear, s.seconds_update], dtype=torch.float64, device="cuda")

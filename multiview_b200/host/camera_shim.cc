@@ -2,6 +2,7 @@
 #include <string>
 
 #include "camera_params.h"
+#include "rpc_pairs.h"
 
 static thread_local std::string g_cam_err;
 
@@ -46,6 +47,21 @@ int mvh_camera_convert(const int* size, const double* focal, const double* cente
     }
     if (mean_focal) *mean_focal = cp.GetFocalLength();
     return 0;
+  } catch (const std::exception& e) { g_cam_err = e.what(); return -1; }
+}
+// genUndistDistPairs: returns the number of pairs kept (<= num_samples^2), -1 on error; the outputs hold 2 doubles per pair
+int mvh_gen_undist_dist_pairs(const int* size, const double* focal, const double* center, const double* dist, int nd, const int* undist_size,
+                              const int* crop_size, int num_samples, double* undist_centered, double* dist_centered) {
+  try {
+    using namespace camera;
+    CameraParameters cp(Vector2i(size[0], size[1]), Vector2d(focal[0], focal[1]), Vector2d(center[0], center[1]),
+                        std::vector<double>(dist, dist + nd));
+    if (undist_size) cp.SetUndistortedSize(Vector2i(undist_size[0], undist_size[1]));
+    if (crop_size) cp.SetDistortedCropSize(Vector2i(crop_size[0], crop_size[1]));
+    std::vector<double> u, d;
+    mvba_host::gen_undist_dist_pairs(num_samples, cp, &u, &d);
+    for (size_t i = 0; i < u.size(); i++) { undist_centered[i] = u[i]; dist_centered[i] = d[i]; }
+    return (int)(u.size() / 2);
   } catch (const std::exception& e) { g_cam_err = e.what(); return -1; }
 }
 }

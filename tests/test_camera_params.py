@@ -92,3 +92,22 @@ def test_undeclared_conversion_and_bad_distortion_length_are_errors(host):
         convert(host, (640, 480), 600.0, (320, 240), [], RAW, UNDISTORTED, np.zeros((1, 2)))
     with pytest.raises(RuntimeError, match="irregular distortion vector size"):
         convert(host, (640, 480), 600.0, (320, 240), [0.1, 0.2, 0.3], UNDISTORTED_C, DISTORTED, np.zeros((1, 2)))
+
+
+def test_rpc_sample_pairs_follow_gen_undist_dist_pairs(host):
+    """genUndistDistPairs (rpc_distortion.cc:497-553) replayed in numpy on top of the UNDISTORTED -> DISTORTED conversion."""
+    size, focal, center = (224, 171), 210.0, (112.25, 85.5)
+    dist = [-0.25, 0.08, 0.0012, -0.0008]; usize, crop, ns = (300, 240), (200, 150), 25
+    sz = np.asarray(size, np.int32); fo = np.asarray([focal, focal]); ce = np.asarray(center); di = np.asarray(dist)
+    us = np.asarray(usize, np.int32); cr = np.asarray(crop, np.int32)
+    u_out = np.zeros(2 * ns * ns); d_out = np.zeros(2 * ns * ns)
+    n = host.mvh_gen_undist_dist_pairs(sz.ctypes.data_as(ip), fo.ctypes.data_as(dp), ce.ctypes.data_as(dp), di.ctypes.data_as(dp), 4,
+                                       us.ctypes.data_as(ip), cr.ctypes.data_as(ip), ns, u_out.ctypes.data_as(dp), d_out.ctypes.data_as(dp))
+    xs = (usize[0] - 1.0) * np.arange(ns) / (ns - 1.0); ys = (usize[1] - 1.0) * np.arange(ns) / (ns - 1.0)
+    X, Y = np.meshgrid(xs, ys, indexing="ij")
+    und = np.stack([X.ravel(), Y.ravel()], 1)
+    dis = convert(host, size, focal, center, dist, UNDISTORTED, DISTORTED, und, undist_size=usize)
+    keep = (np.abs(dis[:, 0] - size[0] / 2.0) <= crop[0] / 2.0) & (np.abs(dis[:, 1] - size[1] / 2.0) <= crop[1] / 2.0)
+    assert 0 < keep.sum() < ns * ns and n == keep.sum()
+    assert np.array_equal(u_out[:2 * n].reshape(-1, 2), und[keep] - np.asarray(usize) / 2.0)
+    assert np.array_equal(d_out[:2 * n].reshape(-1, 2), dis[keep] - np.asarray(size) / 2.0)
