@@ -3,6 +3,7 @@
 
 #include "camera_params.h"
 #include "rpc_pairs.h"
+#include "pass_utils.h"
 
 static thread_local std::string g_cam_err;
 
@@ -63,5 +64,19 @@ int mvh_gen_undist_dist_pairs(const int* size, const double* focal, const double
     for (size_t i = 0; i < u.size(); i++) { undist_centered[i] = u[i]; dist_centered[i] = d[i]; }
     return (int)(u.size() / 2);
   } catch (const std::exception& e) { g_cam_err = e.what(); return -1; }
+}
+// depthValue for n pixels of one cloud: has[i] / xyz[3 i]; -1 when a pixel is out of range (the reference aborts)
+int mvh_depth_values(const float* cloud, int rows, int cols, int n, const double* dist_ip, unsigned char* has, double* xyz) {
+  try {
+    for (int i = 0; i < n; i++) has[i] = mvba_host::depth_value(cloud, rows, cols, dist_ip + 2 * i, xyz + 3 * i) ? 1 : 0;
+    return 0;
+  } catch (const std::exception& e) { g_cam_err = e.what(); return -1; }
+}
+// compact_observations: returns the number of inliers; outputs sized for n
+long long mvh_compact_observations(long long n, const int* pid, const int* cid, const float* pix, const unsigned char* inlier, int* opid, int* ocid,
+                                   float* opix, long long* source) {
+  mvba_host::Observations o = mvba_host::compact_observations(n, pid, cid, pix, nullptr, nullptr, nullptr, nullptr, inlier);
+  for (size_t i = 0; i < o.pid.size(); i++) { opid[i] = o.pid[i]; ocid[i] = o.cid[i]; opix[2 * i] = o.pix[2 * i]; opix[2 * i + 1] = o.pix[2 * i + 1]; source[i] = o.source[i]; }
+  return (long long)o.pid.size();
 }
 }

@@ -111,3 +111,42 @@ def test_rpc_sample_pairs_follow_gen_undist_dist_pairs(host):
     assert 0 < keep.sum() < ns * ns and n == keep.sum()
     assert np.array_equal(u_out[:2 * n].reshape(-1, 2), und[keep] - np.asarray(usize) / 2.0)
     assert np.array_equal(d_out[:2 * n].reshape(-1, 2), dis[keep] - np.asarray(size) / 2.0)
+
+
+def test_depth_value_lookup(host):
+    """depthValue (dense_map_utils.cc:1362-1391): nearest pixel with C round(), zero triple = no measurement, hitting the far
+    bound after rounding = no measurement, beyond it = the reference aborts."""
+    rows, cols = 4, 6
+    cloud = np.arange(rows * cols * 3, dtype=np.float32).reshape(rows, cols, 3) + 1.0
+    cloud[2, 3] = 0.0
+    fp, ucp = C.POINTER(C.c_float), C.POINTER(C.c_ubyte)
+    pix = np.array([[0.0, 0.0], [2.4, 1.6], [2.5, 0.5], [3.2, 1.9], [5.49, 3.49], [5.5, 1.0], [1.0, 3.5], [0.49, 0.49]])
+    has = np.zeros(len(pix), np.uint8); xyz = np.zeros((len(pix), 3))
+    assert host.mvh_depth_values(cloud.ctypes.data_as(fp), rows, cols, len(pix), pix.ctypes.data_as(dp), has.ctypes.data_as(ucp), xyz.ctypes.data_as(dp)) == 0
+    # round half away from zero: (2.5, 0.5) -> col 3, row 1
+    want_rc = [(0, 0), (2, 2), (1, 3), None, (3, 5), None, None, (0, 0)]
+    for i, rc in enumerate(want_rc):
+        if rc is None:
+            assert has[i] == 0 and (xyz[i] == 0).all()
+        else:
+            assert has[i] == 1 and np.array_equal(xyz[i], cloud[rc].astype(np.float64))
+    bad = np.array([[6.6, 1.0]])
+    assert host.mvh_depth_values(cloud.ctypes.data_as(fp), rows, cols, 1, bad.ctypes.data_as(dp), has.ctypes.data_as(ucp), xyz.ctypes.data_as(dp)) == -1
+    assert b"Out of range in the depth cloud" in host.mvh_camera_last_error()
+    # empty cloud
+    assert host.mvh_depth_values(None, 0, 0, 1, pix.ctypes.data_as(dp), has.ctypes.data_as(ucp), xyz.ctypes.data_as(dp)) == 0 and has[0] == 0
+
+
+def test_compact_observations_keeps_order_and_ids(host):
+    rng = np.random.default_rng(5)
+    n = 200
+    pid = np.sort(rng.integers(0, 40, n)).astype(np.int32); cid = rng.integers(0, 12, n).astype(np.int32)
+    pix = rng.uniform(0, 500, (n, 2)).astype(np.float32); inl = (rng.random(n) > 0.3).astype(np.uint8)
+    opid = np.zeros(n, np.int32); ocid = np.zeros(n, np.int32); opix = np.zeros((n, 2), np.float32); src = np.zeros(n, np.int64)
+    host.mvh_compact_observations.restype = C.c_longlong
+    k = host.mvh_compact_observations(C.c_longlong(n), pid.ctypes.data_as(ip), cid.ctypes.data_as(ip), pix.ctypes.data_as(C.POINTER(C.c_float)),
+                                      inl.ctypes.data_as(C.POINTER(C.c_ubyte)), opid.ctypes.data_as(ip), ocid.ctypes.data_as(ip),
+                                      opix.ctypes.data_as(C.POINTER(C.c_float)), src.ctypes.data_as(C.POINTER(C.c_longlong)))
+    sel = np.flatnonzero(inl)
+    assert k == len(sel) and np.array_equal(src[:k], sel)
+    assert np.array_equal(opid[:k], pid[sel]) and np.array_equal(ocid[:k], cid[sel]) and np.array_equal(opix[:k], pix[sel])
