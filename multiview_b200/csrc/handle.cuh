@@ -75,7 +75,8 @@ struct mvba_problem {
   std::vector<int64_t> h_trk_obs0, h_trk_dtri0, h_trk_dmesh0, h_trk_pm0, h_trk_pt0;
   std::vector<int32_t> h_cam_p0, h_cam_p1, h_pose_col;
   std::vector<double> h_cam_bs, h_cam_es;
-  std::vector<double> h_x;             // staging for the parameter vector
+  std::vector<double> h_x;             // staging for the parameter vector (page-locked once sized: setup.cuh)
+  bool h_x_pinned = false;
   std::vector<double> h_lo, h_hi;      // per-scalar bounds (only offsets are ever bounded)
   std::vector<int32_t> h_xcol;         // parameter scalar -> free index (f cols, then nf + 3*pid) or -1
   bool bounded = false;

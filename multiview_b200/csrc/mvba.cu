@@ -70,6 +70,7 @@ int mvba_create(const mvba_config* cfg, int device, mvba_problem** out) {
 int mvba_destroy(mvba_problem* h) {
   if (!h) return MVBA_OK;
   if (h->solver) { cudaSetDevice(h->device); solver_destroy(h); }
+  if (h->h_x_pinned) { cudaSetDevice(h->device); cudaHostUnregister(h->h_x.data()); h->h_x_pinned = false; }
   if (h->stream) { cudaSetDevice(h->device); cudaStreamDestroy(h->stream); }
   delete h;
   return MVBA_OK;

@@ -2,6 +2,7 @@
 // residual-block order and row layout (reference rig_calibrator.cc:1614-1903), parameter-block
 // constancy (:1702-1752, 1787-1793, 1834-1839) and the reduced-system column numbering.
 #pragma once
+#include <thread>
 #include <algorithm>
 #include <cmath>
 
@@ -217,12 +218,32 @@ inline int setup(mvba_problem* h) {
   v.depth_xyz = h->d_depth.p; v.mesh_xyz = h->d_mesh.p;
   v.prior_pid = h->d_prior_pid.p; v.prior_ref = h->d_prior_ref.p; v.prior_w = h->d_prior_w.p; v.prior_th = h->d_prior_th.p; v.prior_row0 = h->d_prior_row0.p;
   v.trk_obs0 = h->d_trk_obs0.p; v.trk_dtri0 = h->d_trk_dtri0.p; v.trk_dmesh0 = h->d_trk_dmesh0.p; v.trk_pm0 = h->d_trk_pm0.p; v.trk_pt0 = h->d_trk_pt0.p;
+  if (h->h_x_pinned) { cudaHostUnregister(h->h_x.data()); h->h_x_pinned = false; }
   h->h_x.assign(v.nx, 0.0);
+  // page-lock the staging vector: the parameter upload / write-back of every mvba_solve then runs at full PCIe rate
+  if (v.nx > 0 && cudaHostRegister(h->h_x.data(), sizeof(double) * v.nx, cudaHostRegisterDefault) == cudaSuccess) h->h_x_pinned = true;
+  else cudaGetLastError();
   h->built = true;
   return MVBA_OK;
 }
 
 // Caller arrays -> staging -> device parameter vector.
+// memcpy of a large array on a few host threads (the landmark block of the parameter vector is tens of MB per solve)
+inline void big_copy(void* dst, const void* src, size_t bytes) {
+  const size_t min_chunk = (size_t)2 << 20;
+  int nt = (int)std::min<size_t>(8, bytes / min_chunk);
+  if (nt <= 1) { std::memcpy(dst, src, bytes); return; }
+  std::vector<std::thread> th;
+  const size_t per = ((bytes / nt) + 63) & ~(size_t)63;
+  for (int t = 0; t < nt; t++) {
+    const size_t o = (size_t)t * per;
+    if (o >= bytes) break;
+    const size_t len = std::min(per, bytes - o);
+    th.emplace_back([=]() { std::memcpy((char*)dst + o, (const char*)src + o, len); });
+  }
+  for (auto& t : th) t.join();
+}
+
 inline int upload_params(mvba_problem* h) {
   const View& v = h->view;
   const mvba_params& p = h->prm;
@@ -247,7 +268,7 @@ inline int upload_params(mvba_problem* h) {
     else { for (int k = 0; k < nd2i; k++) x[s.x_d2i + k] = 0; if (nd2i == 7) x[s.x_d2i + 6] = 1; }
     x[s.x_scale] = p.depth_scale ? p.depth_scale[t] : 1.0;
   }
-  std::memcpy(x + v.x_xyz, p.xyz, sizeof(double) * 3 * v.P);
+  big_copy(x + v.x_xyz, p.xyz, sizeof(double) * 3 * v.P);
   MVBA_CUDA(cudaMemcpyAsync(h->d_x.p, x, sizeof(double) * v.nx, cudaMemcpyHostToDevice, h->stream));
   return MVBA_OK;
 }
@@ -270,7 +291,7 @@ inline int download_params(mvba_problem* h) {
     if (p.depth_to_image) std::memcpy(p.depth_to_image + v.nd2i * t, x + s.x_d2i, v.nd2i * sizeof(double));
     if (p.depth_scale) p.depth_scale[t] = x[s.x_scale];
   }
-  std::memcpy(p.xyz, x + v.x_xyz, sizeof(double) * 3 * v.P);
+  big_copy(p.xyz, x + v.x_xyz, sizeof(double) * 3 * v.P);
   return MVBA_OK;
 }
 
