@@ -82,6 +82,7 @@ struct BacksubArgs {
 #define MVBA_MAXDZ 64  // nd_nz <= MVBA_MAX_DISTORTION / 2
 
 // F y_f of one residual block (rows scaled by sqrt(rho')) from the direction tables.
+template <bool DZ>
 __device__ __forceinline__ void item_dir(const View& v, const BacksubArgs& a, const Item& it, double sr, const double* jd0,
                                          const double* jd1, double* fy) {
   const CamDir& d = a.cd[it.cid];
@@ -100,7 +101,7 @@ __device__ __forceinline__ void item_dir(const View& v, const BacksubArgs& a, co
     fy[0] = it.A[0] * dx[0] + it.A[1] * dx[1] + it.A[2] * dx[2] + it.Jf[0] * df + it.Jc * dcx;
     fy[1] = it.A[3] * dx[0] + it.A[4] * dx[1] + it.A[5] * dx[2] + it.Jf[1] * df + it.Jc * dcy;
     fy[2] = 0;
-    if (s.c_dist >= 0) {
+    if (DZ && s.c_dist >= 0) {
       for (int k = 0; k < s.nd_nz; k++) {
         const double dk = dir_at(a.yf, a.jscale_f, s.c_dist + k);
         fy[0] += jd0[k] * dk; fy[1] += jd1[k] * dk;
@@ -124,9 +125,12 @@ __device__ __forceinline__ void item_dir(const View& v, const BacksubArgs& a, co
   }
 }
 
-__global__ void __launch_bounds__(128) backsub_kernel(View v, BacksubArgs a) {
+// DZ: some sensor's distortion coefficients float (their Jacobian columns are needed, dynamically indexed -> local memory);
+// without it the whole residual block stays in registers.
+template <bool DZ>
+__global__ void __launch_bounds__(128, 4) backsub_kernel(View v, BacksubArgs a) {
   double mcc = 0;
-  double jd[2 * MVBA_MAXDZ];
+  double jd[DZ ? 2 * MVBA_MAXDZ : 2];
   for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < v.P; p += gridDim.x * blockDim.x) {
     const int64_t r0[5] = {v.trk_obs0[p], v.trk_dtri0[p], v.trk_dmesh0[p], v.trk_pm0[p], v.trk_pt0[p]};
     const int64_t r1[5] = {v.trk_obs0[p + 1], v.trk_dtri0[p + 1], v.trk_dmesh0[p + 1], v.trk_pm0[p + 1], v.trk_pt0[p + 1]};
@@ -134,24 +138,29 @@ __global__ void __launch_bounds__(128) backsub_kernel(View v, BacksubArgs a) {
     double se[3] = {1, 1, 1};
     if (a.jscale_e) { se[0] = a.jscale_e[3 * (size_t)p]; se[1] = a.jscale_e[3 * (size_t)p + 1]; se[2] = a.jscale_e[3 * (size_t)p + 2]; }
     double u[3] = {0, 0, 0}, H0[6] = {0, 0, 0, 0, 0, 0}, s1 = 0, s2 = 0;
+#pragma unroll
     for (int kind = 0; kind < 5; kind++) {
       for (int64_t j = r0[kind]; j < r1[kind]; j++) {
         Item it;
-        if (kind == 0) eval_cam<true>(v, a.x, a.tab, j, it, jd, jd + MVBA_MAXDZ);
+        if (kind == 0) eval_cam<true>(v, a.x, a.tab, j, it, DZ ? jd : nullptr, DZ ? jd + MVBA_MAXDZ : nullptr);
         else if (kind == 1) eval_depth(v, a.x, a.tab, a.dtab, MVBA_BLOCK_DEPTH_TRI, j, it);
         else if (kind == 2) eval_depth(v, a.x, a.tab, a.dtab, MVBA_BLOCK_DEPTH_MESH, j, it);
         else eval_prior(v, a.x, j, it);
-        double s = 0;
-        for (int k = 0; k < it.nr; k++) s += it.r[k] * it.r[k];
+        const int nr = kind == 0 ? 2 : 3;  // == it.nr, known per kind so that the rows are indexed statically
+        double s = it.r[0] * it.r[0] + it.r[1] * it.r[1];
+        if (nr == 3) s += it.r[2] * it.r[2];
         double hr, sr;
         cauchy(it.loss_a, s, &hr, &sr);
         double fy[3] = {0, 0, 0};
-        if (kind < 3) item_dir(v, a, it, sr, jd, jd + MVBA_MAXDZ, fy);
-        for (int r = 0; r < it.nr; r++) {
-          const double e0 = sr * it.E[3 * r] * se[0], e1 = sr * it.E[3 * r + 1] * se[1], e2 = sr * it.E[3 * r + 2] * se[2];
-          H0[0] += e0 * e0; H0[1] += e0 * e1; H0[2] += e0 * e2; H0[3] += e1 * e1; H0[4] += e1 * e2; H0[5] += e2 * e2;
-          u[0] += e0 * fy[r]; u[1] += e1 * fy[r]; u[2] += e2 * fy[r];
-          s1 += fy[r] * (sr * it.r[r]); s2 += fy[r] * fy[r];
+        if (kind < 3) item_dir<DZ>(v, a, it, sr, jd, jd + (DZ ? MVBA_MAXDZ : 0), fy);
+#pragma unroll
+        for (int r = 0; r < 3; r++) {
+          if (r < nr) {
+            const double e0 = sr * it.E[3 * r] * se[0], e1 = sr * it.E[3 * r + 1] * se[1], e2 = sr * it.E[3 * r + 2] * se[2];
+            H0[0] += e0 * e0; H0[1] += e0 * e1; H0[2] += e0 * e2; H0[3] += e1 * e1; H0[4] += e1 * e2; H0[5] += e2 * e2;
+            u[0] += e0 * fy[r]; u[1] += e1 * fy[r]; u[2] += e2 * fy[r];
+            s1 += fy[r] * (sr * it.r[r]); s2 += fy[r] * fy[r];
+          }
         }
       }
     }

@@ -294,7 +294,9 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
     std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return trk_umin[a] < trk_umin[b]; });
     std::vector<int32_t> t0, tw0, twn;
     // at least ~6 tiles per CTA so that the static tile -> CTA assignment balances (small shards of a multi-GPU run)
-    const int tile_max = (int)std::max<size_t>(48, std::min<size_t>(512, order.size() / (size_t)(6 * std::max(h->sm_count, 1))));
+    int tile_div = 6;  // tiles per SM (tuning knob: MVBA_TILE_DIV)
+    if (const char* ev = std::getenv("MVBA_TILE_DIV")) { const int d = std::atoi(ev); if (d >= 1 && d <= 64) tile_div = d; }
+    const int tile_max = (int)std::max<size_t>(48, std::min<size_t>(512, order.size() / (size_t)(tile_div * std::max(h->sm_count, 1))));
     size_t i = 0;
     int wn_max = 0;
     while (i < order.size()) {

@@ -232,7 +232,10 @@ inline int solver_solve(mvba_problem* h, const mvba_solve_options& o, mvba_summa
       b.x = h->d_x.p; b.tab = h->d_tab.p; b.dtab = h->d_dtab.p; b.cd = s->camdir.p; b.sdir = s->sensdir.p;
       b.jscale_f = scaled ? s->jscale_f.p : nullptr; b.jscale_e = scaled ? s->jscale_e.p : nullptr;
       b.Hinv = s->Hinv.p; b.ge = s->ge.p; b.yf = s->y.p; b.ye = s->ye.p; b.lm = s->lm.p; b.lm_mcc = LM_MCC;
-      backsub_kernel<<<s->grid_backsub, 128, 0, h->stream>>>(v, b);
+      bool dz = false;
+      for (int t = 0; t < v.T; t++) dz = dz || v.sens[t].c_dist >= 0;
+      if (dz) backsub_kernel<true><<<s->grid_backsub, 128, 0, h->stream>>>(v, b);
+      else backsub_kernel<false><<<s->grid_backsub, 128, 0, h->stream>>>(v, b);
       h->launches += 2;
     }
     update_kernel<<<(v.nx + tb - 1) / tb, tb, 0, h->stream>>>(v.nx, s->nf, s->xcol.p, h->d_x.p, s->y.p, s->ye.p, scaled ? s->jscale_f.p : nullptr,
