@@ -39,7 +39,7 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", type=int, default=5)
     ap.add_argument("--scale", type=float, default=1.0, help="shrink the workload (debug only; invalidates the number)")
-    ap.add_argument("--cpu-sample", type=float, default=0.1, help="fraction of the workload timed on the CPU")
+    ap.add_argument("--cpu-sample", type=float, default=0.25, help="fraction of the workload timed on the CPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--preconditioner", type=int, default=0)
     return ap.parse_args()
@@ -110,7 +110,7 @@ def algorithmic_bytes(pr):
     return b_rj, b_schur, float(pf.mean())
 
 
-def cpu_baseline(pr_full, frac, jac_mode=0, iters=3):
+def cpu_baseline(pr_full, frac, jac_mode=0, iters=5):
     """Times the oracle's Ceres-style LM (numeric-diff Jacobians as the reference incurs them) on a
     bounded sample and scales to the full workload by observation count."""
     from multiview_b200 import _abi, synth

@@ -103,9 +103,9 @@ inline int run_pcg(mvba_problem* h, const mvba_solve_options& o, int* iters_out)
     void* args[] = {&s->R, &s->A, &Mpp, &Mbb, &bb, &xx, &rr, &zz, &pp, &qq, &sc, &eta, &min_it, &mx};
     MVBA_CUDA(cudaLaunchCooperativeKernel((const void*)pcg_fused_kernel, dim3(s->pcg_coop_grid), dim3(256), args, 0, h->stream));
     h->launches++;
+    // the iteration count lands in pinned memory; the caller reads it after the LM iteration's own synchronisation (-1: deferred)
     MVBA_CUDA(cudaMemcpyAsync(s->flags_host, s->pcg_flags.p, 2 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
-    MVBA_CUDA(cudaStreamSynchronize(h->stream));
-    *iters_out = s->flags_host[1];
+    *iters_out = -1;
     return MVBA_OK;
   }
   pcg_init_kernel<<<gb, tb, 0, h->stream>>>(nf, s->npc, s->R.rhs, s->y.p, s->r.p, s->q.p, sc);
@@ -218,7 +218,6 @@ inline int solver_solve(mvba_problem* h, const mvba_solve_options& o, mvba_summa
     tm.begin(PH_LINEAR);
     int cgit = 0;
     rc = run_pcg(h, o, &cgit); if (rc) return rc;
-    nlin += cgit;
     tm.end();
     // ---- back-substitution, candidate point and its cost ----
     tm.begin(PH_UPDATE);
@@ -251,6 +250,8 @@ inline int solver_solve(mvba_problem* h, const mvba_solve_options& o, mvba_summa
     tm.end();
     MVBA_CUDA(cudaStreamSynchronize(h->stream));
     MVBA_CUDA(cudaGetLastError());
+    if (cgit < 0) cgit = s->flags_host[1];
+    nlin += cgit;
     mvba_iteration rec = *s->rec;
     int dev_term = rec.linear_iterations;
     rec.linear_iterations = cgit;

@@ -81,6 +81,20 @@ def test_argument_validation(product_lib):
     assert product_lib.mvba_destroy(h) == 0
 
 
+def test_rpc_fit_argument_validation_and_no_device(product_lib):
+    """mvba_rpc_fit rejects bad sizes before touching the device, and has no CPU fallback."""
+    dp = C.POINTER(C.c_double)
+    xy = np.zeros((4, 2)); c = np.zeros(_abi.rpc_num_params(1)); st = np.zeros(4)
+    args = lambda n, deg, it: (C.c_int32(0), C.c_int64(n), xy.ctypes.data_as(dp), xy.ctypes.data_as(dp), C.c_int32(deg), C.c_int32(it),
+                               C.c_double(1e-12), C.c_int32(0), c.ctypes.data_as(dp), st.ctypes.data_as(dp))
+    for bad in (args(0, 1, 10), args(4, 0, 10), args(4, 7, 10), args(4, 1, -1)):
+        assert product_lib.mvba_rpc_fit(*bad) == -1
+        assert b"mvba_rpc_fit" in product_lib.mvba_last_error()
+    assert product_lib.mvba_rpc_fit(C.c_int32(0), C.c_int64(4), None, xy.ctypes.data_as(dp), 1, 10, C.c_double(1e-12), 0, c.ctypes.data_as(dp), None) == -1
+    if product_lib.mvba_device_count() == 0:
+        assert product_lib.mvba_rpc_fit(*args(4, 1, 10)) == -2      # MVBA_ENODEVICE
+
+
 # ---------------------------------------------------------------------------------------------
 # oracle self-consistency
 # ---------------------------------------------------------------------------------------------
