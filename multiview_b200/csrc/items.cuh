@@ -29,13 +29,20 @@ struct Item {
   double weight;
 };
 
-__device__ __forceinline__ void load_camtab(const CamTab* __restrict__ tab, int cid, const double* X, double* Xc, double* Z) {
-  const double* R = tab[cid].R;
-  const double* t = tab[cid].t;
+// R (9) and t (3) of one camera image are the first 12 doubles of its 560-byte CamTab row: six 128-bit loads instead of
+// twelve 64-bit ones (these gathers are divergent across a warp, so every request costs a sector).
+__device__ __forceinline__ void load_rt(const CamTab* __restrict__ tab, int cid, double* rt) {
+  const double2* q = reinterpret_cast<const double2*>(tab + cid);
+#pragma unroll
+  for (int k = 0; k < 6; k++) { const double2 v2 = __ldg(q + k); rt[2 * k] = v2.x; rt[2 * k + 1] = v2.y; }
+}
+
+__device__ __forceinline__ void load_camtab(const CamTab* __restrict__ tab, int cid, const double* X, double* Xc, double* Z, double* rt) {
+  load_rt(tab, cid, rt);
 #pragma unroll
   for (int i = 0; i < 3; i++) {
-    Z[i] = __ldg(R + 3 * i) * X[0] + __ldg(R + 3 * i + 1) * X[1] + __ldg(R + 3 * i + 2) * X[2];
-    Xc[i] = Z[i] + __ldg(t + i);
+    Z[i] = rt[3 * i] * X[0] + rt[3 * i + 1] * X[1] + rt[3 * i + 2] * X[2];
+    Xc[i] = Z[i] + rt[9 + i];
   }
 }
 
@@ -46,16 +53,24 @@ __device__ inline void eval_cam(const View& v, const double* __restrict__ x, con
   it.cid = v.cid[i]; it.pid = v.pid[i]; it.sensor = v.cam_sensor[it.cid];
   const double* X = x + v.x_xyz + 3 * (int64_t)it.pid;
   double Xw[3] = {X[0], X[1], X[2]};
-  load_camtab(tab, it.cid, Xw, it.Xc, it.Z);
+  {
+    double rt[12];
+    load_camtab(tab, it.cid, Xw, it.Xc, it.Z, rt);
+  }
   project_distort<WANT_J>(v.sens[it.sensor], x, it.Xc, v.pix[i], it.r, it.A, it.Jf, &it.Jc, Jd0, Jd1);
   it.r[2] = 0;
   if (WANT_J) {
-    const double* R = tab[it.cid].R;
+    double rt[10];  // R again (L1 hit) rather than 9 registers held across the projection
+    {
+      const double2* q = reinterpret_cast<const double2*>(tab + it.cid);
+#pragma unroll
+      for (int k = 0; k < 5; k++) { const double2 v2 = __ldg(q + k); rt[2 * k] = v2.x; rt[2 * k + 1] = v2.y; }
+    }
 #pragma unroll
     for (int a = 0; a < 2; a++)
 #pragma unroll
       for (int b = 0; b < 3; b++)
-        it.E[3 * a + b] = it.A[3 * a] * __ldg(R + b) + it.A[3 * a + 1] * __ldg(R + 3 + b) + it.A[3 * a + 2] * __ldg(R + 6 + b);
+        it.E[3 * a + b] = it.A[3 * a] * rt[b] + it.A[3 * a + 1] * rt[3 + b] + it.A[3 * a + 2] * rt[6 + b];
   }
   it.loss_a = v.robust_th; it.weight = 1.0;
 }

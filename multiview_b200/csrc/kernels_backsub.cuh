@@ -14,7 +14,8 @@
 
 namespace mvba {
 
-struct CamDir { double a[3], w[3], wrc[3]; };
+struct alignas(16) CamDir { double a[3], w[3], wrc[3], trc[3]; };  // 96 bytes: gathered per residual block as six 128-bit loads
+static_assert(sizeof(CamDir) == 96, "CamDir layout");
 struct SensDir { double td[3], wd[3], ds, dA[12]; };
 
 __device__ __forceinline__ double dir_at(const double* __restrict__ yf, const double* __restrict__ sf, int gc) {
@@ -47,6 +48,7 @@ __global__ void dir_cameras_kernel(View v, const CamTab* __restrict__ tab, const
       o.w[i] = ct.W0[4 * i] * d0[3] + ct.W0[4 * i + 1] * d0[4] + ct.W0[4 * i + 2] * d0[5] + ct.W0[4 * i + 3] * d0[6] +
                ct.W1[4 * i] * d1[3] + ct.W1[4 * i + 1] * d1[4] + ct.W1[4 * i + 2] * d1[5] + ct.W1[4 * i + 3] * d1[6] + doff * ct.wa[i];
       o.wrc[i] = ct.Wrc[4 * i] * dr[3] + ct.Wrc[4 * i + 1] * dr[4] + ct.Wrc[4 * i + 2] * dr[5] + ct.Wrc[4 * i + 3] * dr[6];
+      o.trc[i] = ct.trc[i];
     }
     cd[c] = o;
   } else if (c < v.C + v.T) {
@@ -85,15 +87,19 @@ struct BacksubArgs {
 template <bool DZ>
 __device__ __forceinline__ void item_dir(const View& v, const BacksubArgs& a, const Item& it, double sr, const double* jd0,
                                          const double* jd1, double* fy) {
-  const CamDir& d = a.cd[it.cid];
-  const double* trc = a.tab[it.cid].trc;
-  const double y[3] = {it.Xc[0] - __ldg(trc), it.Xc[1] - __ldg(trc + 1), it.Xc[2] - __ldg(trc + 2)};
+  double dd[12];  // a | w | wrc | trc of the block's camera image
+  {
+    const double2* q = reinterpret_cast<const double2*>(a.cd + it.cid);
+#pragma unroll
+    for (int k = 0; k < 6; k++) { const double2 v2 = __ldg(q + k); dd[2 * k] = v2.x; dd[2 * k + 1] = v2.y; }
+  }
+  const double y[3] = {it.Xc[0] - dd[9], it.Xc[1] - dd[10], it.Xc[2] - dd[11]};
   double dx[3], c1[3], c2[3];
-  const double w[3] = {d.w[0], d.w[1], d.w[2]}, wr[3] = {d.wrc[0], d.wrc[1], d.wrc[2]};
+  const double w[3] = {dd[3], dd[4], dd[5]}, wr[3] = {dd[6], dd[7], dd[8]};
   cross3(w, it.Z, c1);
   cross3(wr, y, c2);
 #pragma unroll
-  for (int i = 0; i < 3; i++) dx[i] = d.a[i] + c1[i] + c2[i];
+  for (int i = 0; i < 3; i++) dx[i] = dd[i] + c1[i] + c2[i];
   const SensorDev& s = v.sens[it.sensor];
   if (it.kind == MVBA_BLOCK_CAM) {
     const double df = dir_at(a.yf, a.jscale_f, s.c_focal);
