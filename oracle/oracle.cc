@@ -1038,5 +1038,24 @@ int oracle_rpc_fit(int64_t n, const double* in_xy, const double* out_xy, int32_t
   if (stats) { stats[0] = st.initial_cost; stats[1] = st.final_cost; stats[2] = st.iterations; stats[3] = st.successful; }
   return 0;
 }
+// float32 rays against a mesh: the restated triangle test over all triangles (checked against the reference's BVHTree in tests/)
+int64_t oracle_ray_mesh(int64_t nv, const float* verts, int64_t nf, const uint32_t* faces, int64_t n, const float* origin, const float* dir,
+                        float tmin, float tmax, uint8_t* hit, float* t_out) {
+  int64_t hits = 0;
+#pragma omp parallel for reduction(+ : hits) schedule(static)
+  for (int64_t i = 0; i < n; i++) {
+    float best;
+    bool ok = oracle::ray_mesh_nearest(origin + 3 * i, dir + 3 * i, tmin, tmax, verts, faces, nf, &best);
+    hit[i] = ok ? 1 : 0; t_out[i] = best; hits += ok;
+  }
+  return hits;
+}
+// acc::intersect(ray, tri) restated (tracks.h ray_tri) for ONE triangle: 1 and the distance when the hit is accepted
+int oracle_ray_tri(const float* origin, const float* dir, float tmin, float tmax, const float* a, const float* b, const float* c, float* t_out) {
+  float t = 0;
+  bool ok = oracle::ray_tri(origin, dir, tmin, tmax, a, b, c, &t);
+  *t_out = t;
+  return ok ? 1 : 0;
+}
 void oracle_compute_rpc(const double* p, const double* coeffs, int32_t n, double* out) { oracle::compute_rpc(p, coeffs, n, out); }
 }

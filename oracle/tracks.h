@@ -7,8 +7,10 @@
 //   multiViewTriangulation       interest_point.cc:649-722
 //   flagOutlierByExclusionDist   rig_calibrator/bin/rig_calibrator.cc:1003-1038
 //   flagOutliersByTriAngleAndReprojErr  rig_calibrator.cc:1045-1154
-// Included by oracle.cc (needs its Problem / RBlock types).  Parity unpinned by the reference (no tests or fixtures
-// there); pinned against cv2.undistortPoints and a noise-free recovery property in tests/.
+// Included by oracle.cc (needs its Problem / RBlock types).  Triangulation / undistortion / flags: parity unpinned by the reference
+// (no tests or fixtures there); pinned against cv2.undistortPoints and a noise-free recovery property in tests/.  The ray /
+// triangle test IS pinned on the reference: its header-only rayint code compiles here (oracle/ref_build -> oracle/_ref), and
+// tests/test_rayint_pin.py holds ray_tri to it bit for bit (live library + tests/golden/rayint.npz).
 #pragma once
 
 namespace oracle {
@@ -109,6 +111,21 @@ inline bool ray_tri(const float* o, const float* d, float tmin, float tmax, cons
   return -eps <= b0 && b0 <= 1.0f + eps && -eps <= b1 && b1 <= 1.0f + eps && -eps <= b2 && b2 <= 1.0f + eps;
 }
 
+// BVHTree::intersect (rayint/libs/acc/bvh_tree.h:351-405) without the hierarchy: the nearest accepted hit over ALL triangles, tmax
+// shrinking with every hit as the traversal does.  Pinned against the reference's own BVHTree (oracle/_ref/libref_rayint.so,
+// tests/golden/rayint.npz).
+inline bool ray_mesh_nearest(const float* o, const float* d, float tmin, float tmax, const float* verts, const uint32_t* faces, int64_t nfaces,
+                             float* best_out) {
+  float best = std::numeric_limits<float>::infinity();
+  for (int64_t k = 0; k < nfaces; k++) {
+    float t;
+    if (ray_tri(o, d, tmin, tmax, verts + 3 * (size_t)faces[3 * k], verts + 3 * (size_t)faces[3 * k + 1], verts + 3 * (size_t)faces[3 * k + 2], &t) &&
+        !(t > best)) { best = t; tmax = t; }
+  }
+  *best_out = best;
+  return best < std::numeric_limits<float>::infinity();
+}
+
 // ray_mesh_intersect (texture_processing.cc:1436-1479) without an acceleration structure: the nearest accepted hit over
 // ALL triangles, which is what the BVH traversal returns.
 inline bool ray_mesh_brute(const double u[2], double f, const Aff<double>& w2c, const float* verts, const uint32_t* faces, int64_t nfaces,
@@ -122,13 +139,8 @@ inline bool ray_mesh_brute(const double u[2], double f, const Aff<double>& w2c, 
   float o[3] = {(float)ctr[0], (float)ctr[1], (float)ctr[2]}, d[3] = {(float)wr[0], (float)wr[1], (float)wr[2]};
   float dn = std::sqrt(dot3f(d, d));
   for (int a = 0; a < 3; a++) d[a] = d[a] / dn;
-  float tmin = (float)min_dist, tmax = (float)max_dist, best = std::numeric_limits<float>::infinity();
-  for (int64_t k = 0; k < nfaces; k++) {
-    float t;
-    if (ray_tri(o, d, tmin, tmax, verts + 3 * (size_t)faces[3 * k], verts + 3 * (size_t)faces[3 * k + 1], verts + 3 * (size_t)faces[3 * k + 2], &t) &&
-        !(t > best)) { best = t; tmax = t; }
-  }
-  if (!(best < std::numeric_limits<float>::infinity())) return false;
+  float best;
+  if (!ray_mesh_nearest(o, d, (float)min_dist, (float)max_dist, verts, faces, nfaces, &best)) return false;
   for (int a = 0; a < 3; a++) out[a] = ctr[a] + (double)best * wr[a];
   return true;
 }
