@@ -210,3 +210,33 @@ def test_shards_partition_the_tracks_and_sum_to_the_whole(oracle_lib):
         b.close()
     assert seen[0][0] == 0 and seen[-1][1] == pr.num_landmarks and all(seen[i][1] == seen[i + 1][0] for i in range(world - 1))
     assert nres == len(r_all) and abs(costs - c_all) <= 1e-12 * c_all
+
+
+@pytest.mark.parametrize("locality", [False, True])
+def test_both_sharding_modes_partition_the_tracks(locality, oracle_lib):
+    """Input-order and image-ordered landmark ranges: every track on exactly one rank, observation counts balanced, costs add up.
+    Image-ordered shards touch a fraction of the images each -- the case that needs the column layout to be the union over ranks."""
+    pr = synth.make_problem(seed=12, sensors="rig3", num_ref=40, num_landmarks=1500, obs_per_track=5, outlier_frac=0.02)
+    o = _abi.Binding(oracle_lib, "oracle_", pr)
+    c_all, _ = o.evaluate(True)
+    o.close()
+    world = 4
+    owner = np.full(pr.num_landmarks, -1)
+    cost, nobs, images = 0.0, [], []
+    for rank in range(world):
+        q = pr.shard(rank, world, locality=locality)
+        tracks = q.truth["tracks"]
+        assert (owner[tracks] == -1).all()
+        owner[tracks] = rank
+        assert np.allclose(q.xyz.reshape(-1, 3), pr.xyz.reshape(-1, 3)[tracks])
+        b = _abi.Binding(oracle_lib, "oracle_", q)
+        c, _ = b.evaluate(True)
+        b.close()
+        cost += c; nobs.append(q.num_obs); images.append(len(np.unique(q.cid)))
+    assert (owner >= 0).all() and abs(cost - c_all) <= 1e-12 * c_all
+    assert max(nobs) - min(nobs) <= 2 * 5 + 0.02 * pr.num_obs
+    n_img = len(pr.cam_sensor)
+    if locality:
+        assert max(images) < 0.75 * n_img          # a rank sees only part of the images ...
+    else:
+        assert min(images) > 0.9 * n_img           # ... while input-order ranges of random tracks see nearly all of them

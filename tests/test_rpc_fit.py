@@ -62,6 +62,23 @@ def test_oracle_degree_continuation_on_a_radtan_lens(oracle_lib):
     assert np.sqrt(2 * costs[2] / len(u)) < 2.0                   # cubic ratio: under 2 px rms on a strongly distorted lens
 
 
+@pytest.mark.parametrize("deg", [1, 2])
+def test_oracle_fit_is_the_minimum_an_independent_lm_finds(deg, oracle_lib):
+    """MINPACK's Levenberg-Marquardt (scipy.optimize.least_squares, method="lm") on the same residuals: from the identity model it
+    reaches the oracle's cost, and started AT the oracle's coefficients it cannot improve them."""
+    from scipy.optimize import least_squares
+    u = grid(40); d = radtan(u)
+    c, st = _abi.rpc_fit(oracle_lib, "oracle_", u, d, deg, num_iterations=200, num_threads=8)
+    f = lambda x: (rpc_eval(u, x) - d).ravel()
+    T = (deg + 1) * (deg + 2) // 2
+    x0 = np.zeros(_abi.rpc_num_params(deg)); x0[1] = 1.0; x0[2 * T - 1 + 2] = 1.0
+    kw = dict(method="lm", xtol=1e-15, ftol=1e-15, gtol=1e-15, max_nfev=20000, x_scale="jac")
+    from_identity = least_squares(f, x0, **kw)
+    polished = least_squares(f, c, **kw)
+    assert abs(from_identity.cost - st["final_cost"]) <= 1e-5 * st["final_cost"]
+    assert st["final_cost"] - polished.cost <= 1e-9 * st["final_cost"]
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("deg", [1, 2, 3, 4])
 def test_gpu_fit_follows_the_oracle(deg, oracle_lib, product_lib):
