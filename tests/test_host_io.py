@@ -168,3 +168,55 @@ def test_nvm_export_and_round_trip(host, tmp_path):
     for x, y in zip(a, b):
         if x != y:
             assert abs(float(x) - float(y)) <= 1e-12 * max(1.0, abs(float(x)))
+
+
+# ---------------------------------------------------------------------------------------------
+# pinned on the reference's own Python parsers (rig_calibrator/bin/rig_utils.py): tests/golden/host_formats.json holds what
+# parseRigConfig and parse_images_and_camera_poses read back from files written by multiview_b200/host
+# (tools/make_golden_hostio.py); the values must be the ones the files were composed from.
+# ---------------------------------------------------------------------------------------------
+def _check_rig_parse(parsed):
+    want = [("nav_cam", 608.04, [640.5, 480.2], [0.998], "fisheye", (1280, 960), (1200, 900), (1500, 1200), _I, _I, 0.0),
+            ("haz_cam", 210.12345678901234, [112.25, 85.5], [-0.25, 0.08, 0.0012, -0.0008], "radtan", (224, 171), (224, 171), (250, 200),
+             [_c, -_s, 0, _s, _c, 0, 0, 0, 1, 0.05, -0.02, 0.003], [0.99, 0, 0, 0, 0.99, 0, 0, 0, 0.99, 0.001, 0.002, -0.003], 0.0159),
+            ("sci_cam", 1000.0, [668, 501], [], "no_distortion", (1336, 1002), (1336, 1002), (1336, 1002), [1, 0, 0, 0, 1, 0, 0, 0, 1, -0.1, 0, 0], _I,
+             -0.0137)]
+    assert len(parsed) == 3
+    f = lambda v: [float(x) for x in v]
+    for cam, (name, fl, c, dist, kind, size, crop, usize, r2s, d2i, off) in zip(parsed, want):
+        assert cam["sensor_name"] == name and cam["distortion_type"] == kind
+        assert float(cam["focal_length"]) == fl and f(cam["optical_center"]) == list(c) and f(cam["distortion_coeffs"]) == list(dist)
+        assert [int(v) for v in cam["image_size"]] == list(size) and [int(v) for v in cam["distorted_crop_size"]] == list(crop)
+        assert [int(v) for v in cam["undistorted_image_size"]] == list(usize)
+        assert f(cam["ref_to_sensor_transform"]) == [float(v) for v in r2s] and f(cam["depth_to_image_transform"]) == [float(v) for v in d2i]
+        assert float(cam["ref_to_sensor_timestamp_offset"]) == off
+
+
+def test_reference_parsers_read_our_files_golden():
+    import json
+    gold = json.load(open(os.path.join(ROOT, "tests", "golden", "host_formats.json")))
+    _check_rig_parse(gold["rig_config"])
+    rng = np.random.default_rng(3)
+    rows = [rng.normal(size=12) for _ in range(5)]
+    names = [f"data/{['nav_cam', 'haz_cam', 'sci_cam'][i % 3]}/{10000.5 + i:.1f}.jpg" for i in range(5)]
+    for sensor, got in gold["camera_list"].items():
+        idx = [i for i in range(5) if f"/{sensor}/" in names[i]]
+        assert got["images"] == [names[i] for i in idx]
+        for i, M in zip(idx, got["world_to_cam"]):
+            M = np.array(M)
+            assert np.array_equal(M[:3, :3].ravel(), rows[i][:9]) and np.array_equal(M[:3, 3], rows[i][9:]) and np.array_equal(M[3], [0, 0, 0, 1])
+
+
+def test_reference_parser_reads_our_rig_config_live(host, tmp_path):
+    ref_bin = "/root/reference/rig_calibrator/bin"
+    if not os.path.exists(os.path.join(ref_bin, "rig_utils.py")):
+        pytest.skip("the reference is not present on this box; tests/golden/host_formats.json covers this")
+    import sys, warnings
+    sys.path.insert(0, ref_bin)
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        import rig_utils
+    src = tmp_path / "in.txt"; dst = tmp_path / "rig_config.txt"
+    src.write_text(RIG)
+    assert host.mvh_rig_config_roundtrip(str(src).encode(), str(dst).encode(), 1, 1, None) == 0
+    _check_rig_parse(rig_utils.parseRigConfig(str(dst)))
