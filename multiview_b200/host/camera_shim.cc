@@ -4,6 +4,7 @@
 #include "camera_params.h"
 #include "rpc_pairs.h"
 #include "pass_utils.h"
+#include "pose_math.h"
 
 static thread_local std::string g_cam_err;
 
@@ -79,4 +80,15 @@ long long mvh_compact_observations(long long n, const int* pid, const int* cid, 
   for (size_t i = 0; i < o.pid.size(); i++) { opid[i] = o.pid[i]; ocid[i] = o.cid[i]; opix[2 * i] = o.pix[2 * i]; opix[2 * i + 1] = o.pix[2 * i + 1]; source[i] = o.source[i]; }
   return (long long)o.pid.size();
 }
+// world_to_cam of every image (12 doubles each: R row-major, t); -1 when an image falls outside its bracket
+int mvh_world_to_cam_all(int num_cameras, const int* cam_sensor, const int* beg, const int* end, const double* cam_stamp, const double* ref_stamps,
+                         const double* world_to_ref, const double* ref_to_cam, const double* offsets, double* out12) {
+  try {
+    std::vector<mvba_host::Affine> w = mvba_host::world_to_cam_all(num_cameras, cam_sensor, beg, end, cam_stamp, ref_stamps, world_to_ref, ref_to_cam, offsets);
+    for (int c = 0; c < num_cameras; c++) for (int k = 0; k < 12; k++) out12[12 * c + k] = w[c][k];
+    return 0;
+  } catch (const std::exception& e) { g_cam_err = e.what(); return -1; }
+}
+// rigid_transform_to_array(array_to_rigid_transform(a)): the round trip the copy-back performs
+void mvh_rigid_roundtrip(const double* a7, double* out7) { mvba_host::rigid_to_array(mvba_host::array_to_rigid(a7), out7); }
 }

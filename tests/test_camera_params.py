@@ -150,3 +150,36 @@ def test_compact_observations_keeps_order_and_ids(host):
     sel = np.flatnonzero(inl)
     assert k == len(sel) and np.array_equal(src[:k], sel)
     assert np.array_equal(opid[:k], pid[sel]) and np.array_equal(ocid[:k], cid[sel]) and np.array_equal(opix[:k], pix[sel])
+
+
+def test_host_pose_math_matches_scipy_golden_and_flags_bad_brackets(host):
+    """multiview_b200/host/pose_math.h (array_to_rigid_transform, linearInterp, calc_world_to_cam_trans on the host, for the
+    camera list a driver writes after the solve) against tests/golden/pose_interp.npz (scipy Slerp / Rotation)."""
+    g = np.load(os.path.join(GOLD, "pose_interp.npz"))
+    zero, one = np.array([0], np.int32), np.array([1], np.int32)
+    out = np.zeros(12)
+
+    def w2c(b, e, r, bs, es, off, cs):
+        w2r = np.ascontiguousarray(np.concatenate([b, e])); stamps = np.array([bs, es]); cstamp = np.array([cs]); offs = np.array([off])
+        r = np.ascontiguousarray(r)
+        rc = host.mvh_world_to_cam_all(1, zero.ctypes.data_as(ip), zero.ctypes.data_as(ip), one.ctypes.data_as(ip), cstamp.ctypes.data_as(dp),
+                                       stamps.ctypes.data_as(dp), w2r.ctypes.data_as(dp), r.ctypes.data_as(dp), offs.ctypes.data_as(dp), out.ctypes.data_as(dp))
+        return rc, np.concatenate([out[:9].reshape(3, 3), out[9:, None]], axis=1).ravel()      # -> 3x4 row-major like the fixture
+
+    for i in range(len(g["bs"])):
+        rc, m = w2c(g["beg"][i], g["end"][i], g["r2c"][i], g["bs"][i], g["es"][i], g["off"][i], g["cs"][i])
+        assert rc == 0 and np.abs(m - g["world_to_cam"][i]).max() < 1e-11 * max(1.0, np.abs(g["world_to_cam"][i]).max())
+    for i in range(len(g["degenerate"])):                   # beg stamp == end stamp: the beg pose itself
+        rc, m = w2c(g["beg"][i], g["end"][i], g["r2c"][i], 5.0, 5.0, 0.3, 5.0)
+        assert rc == 0 and np.abs(m - g["degenerate"][i]).max() < 1e-12 * max(1.0, np.abs(g["degenerate"][i]).max())
+    p = np.array([0, 0, 0, 0, 0, 0, 1.0])
+    rc, _ = w2c(p, p, p, 10.0, 11.0, 0.0, 11.5)
+    assert rc == -1 and b"Out of bounds in interpolation" in host.mvh_camera_last_error()
+    # array -> transform -> array keeps a unit quaternion (up to the sign Eigen picks) and normalises a scaled one
+    rng = np.random.default_rng(4)
+    for _ in range(20):
+        a = rng.normal(size=7); a[3:] /= np.linalg.norm(a[3:])
+        back = np.zeros(7); scaled = a.copy(); scaled[3:] *= 3.0
+        host.mvh_rigid_roundtrip(scaled.ctypes.data_as(dp), back.ctypes.data_as(dp))
+        s = np.sign(back[3:] @ a[3:])
+        assert np.abs(back[:3] - a[:3]).max() == 0 and np.abs(s * back[3:] - a[3:]).max() < 1e-14
