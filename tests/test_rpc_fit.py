@@ -62,6 +62,33 @@ def test_oracle_degree_continuation_on_a_radtan_lens(oracle_lib):
     assert np.sqrt(2 * costs[2] / len(u)) < 2.0                   # cubic ratio: under 2 px rms on a strongly distorted lens
 
 
+def test_central_difference_of_a_ratio_has_the_closed_form_the_kernel_uses(oracle_lib):
+    """rpc_fit.cuh evaluates d/d den_k as -N m_k / (D^2 - (delta_k m_k)^2) and d/d num_k as m_k / D instead of differencing:
+    here the Ceres-rule quotient (f(c + delta) - f(c - delta)) / (2 delta), delta = max(|c| 1e-6, sqrt(eps)), is formed with the
+    oracle's compute_rpc and compared -- including monomials for which delta * m_k is NOT small against D."""
+    rng = np.random.default_rng(11)
+    deg = 3; T = (deg + 1) * (deg + 2) // 2; n = _abi.rpc_num_params(deg)
+    c = np.zeros(n); c[1] = 1.0; c[2 * T - 1 + 2] = 1.0
+    c += rng.normal(size=n) * np.concatenate([10.0 ** -np.array([0, 1, 1] + [4] * 3 + [7] * 4), 10.0 ** -np.array([3, 3] + [6] * 3 + [9] * 4)] * 2)
+    pts = rng.uniform(-600, 600, (40, 2))
+    mono = np.stack([pts[:, 0] ** (d - i) * pts[:, 1] ** i for d in range(deg + 1) for i in range(d + 1)], 1)
+    N = mono @ c[:T]; D = 1.0 + mono[:, 1:] @ c[T:2 * T - 1]
+    delta = np.maximum(np.abs(c) * 1e-6, np.sqrt(np.finfo(float).eps))
+    worst_linearisation_error = 0.0
+    for k in list(range(0, T, 3)) + list(range(T, 2 * T - 1, 2)):           # x-numerator and x-denominator coefficients
+        cp, cm = c.copy(), c.copy(); cp[k] += delta[k]; cm[k] -= delta[k]
+        fd = (_abi.compute_rpc(oracle_lib, pts, cp)[:, 0] - _abi.compute_rpc(oracle_lib, pts, cm)[:, 0]) / (2 * delta[k])
+        if k < T:
+            closed = mono[:, k] / D
+        else:
+            m = mono[:, k - T + 1]
+            closed = -N * m / (D * D - (delta[k] * m) ** 2)
+            worst_linearisation_error = max(worst_linearisation_error, np.abs(closed / (-N * m / (D * D)) - 1).max())
+        scale = np.abs(closed).max()
+        assert np.abs(fd - closed).max() <= 1e-5 * scale + 1e-9 * np.abs(N / D).max() / delta[k]   # differencing noise: eps |f| / delta
+    assert worst_linearisation_error > 1e-3      # the quotient is NOT the derivative for the high monomials: that is the point
+
+
 @pytest.mark.parametrize("deg", [1, 2])
 def test_oracle_fit_is_the_minimum_an_independent_lm_finds(deg, oracle_lib):
     """MINPACK's Levenberg-Marquardt (scipy.optimize.least_squares, method="lm") on the same residuals: from the identity model it
