@@ -5,6 +5,7 @@
 #include "rpc_pairs.h"
 #include "pass_utils.h"
 #include "pose_math.h"
+#include "bracket.h"
 
 static thread_local std::string g_cam_err;
 
@@ -91,4 +92,24 @@ int mvh_world_to_cam_all(int num_cameras, const int* cam_sensor, const int* beg,
 }
 // rigid_transform_to_array(array_to_rigid_transform(a)): the round trip the copy-back performs
 void mvh_rigid_roundtrip(const double* a7, double* out7) { mvba_host::rigid_to_array(mvba_host::array_to_rigid(a7), out7); }
+// lookup_images_and_brackets over flat arrays: stamps of all sensors concatenated with per-sensor counts.  Outputs are sized by the caller
+// for num_ref * num_sensors entries; returns the number of cameras, -1 on error.
+int mvh_lookup_images_and_brackets(double bracket_len, double max_change, int num_ref, const double* ref_stamps, int num_sensors, const int* counts,
+                                   const double* stamps, const int* cloud_counts, const double* cloud_stamps, const double* offsets, int* sensor,
+                                   int* beg, int* end, double* timestamp, int* image_index, int* cloud_index, double* min_off, double* max_off) {
+  try {
+    std::vector<std::vector<double>> img(num_sensors), cld;
+    size_t o = 0;
+    for (int t = 0; t < num_sensors; t++) { img[t].assign(stamps + o, stamps + o + counts[t]); o += counts[t]; }
+    if (cloud_counts) { cld.resize(num_sensors); o = 0; for (int t = 0; t < num_sensors; t++) { cld[t].assign(cloud_stamps + o, cloud_stamps + o + cloud_counts[t]); o += cloud_counts[t]; } }
+    mvba_host::Bracketing b = mvba_host::lookup_images_and_brackets(bracket_len, max_change, std::vector<double>(ref_stamps, ref_stamps + num_ref), img, cld,
+                                                                    std::vector<double>(offsets, offsets + num_sensors));
+    for (size_t i = 0; i < b.cams.size(); i++) {
+      sensor[i] = b.cams[i].sensor; beg[i] = b.cams[i].beg_ref_index; end[i] = b.cams[i].end_ref_index; timestamp[i] = b.cams[i].timestamp;
+      image_index[i] = b.cams[i].image_index; cloud_index[i] = b.cams[i].cloud_index;
+    }
+    for (int t = 0; t < num_sensors; t++) { min_off[t] = b.min_timestamp_offset[t]; max_off[t] = b.max_timestamp_offset[t]; }
+    return (int)b.cams.size();
+  } catch (const std::exception& e) { g_cam_err = e.what(); return -1; }
+}
 }
