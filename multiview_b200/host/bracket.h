@@ -105,4 +105,17 @@ inline Bracketing lookup_images_and_brackets(double bracket_len, double timestam
   return out;
 }
 
+// lookupImages (dense_map_utils.cc:1745-1805) for the rig case: brackets, at least one image per sensor, cameras in order of their
+// reference-clock time (the reference calls std::sort there; a stable sort is used so that equal times keep the bracket order).
+inline Bracketing lookup_images(double bracket_len, double timestamp_offsets_max_change, const std::vector<double>& ref_timestamps,
+                                const std::vector<std::vector<double>>& image_stamps, const std::vector<std::vector<double>>& cloud_stamps,
+                                const std::vector<double>& ref_to_cam_timestamp_offsets) {
+  Bracketing b = lookup_images_and_brackets(bracket_len, timestamp_offsets_max_change, ref_timestamps, image_stamps, cloud_stamps, ref_to_cam_timestamp_offsets);
+  std::vector<int> count(image_stamps.size(), 0);
+  for (const BracketedImage& c : b.cams) count[c.sensor]++;
+  for (int n : count) if (n == 0) throw std::runtime_error("Could not find images for all sensors. Cannot continue.");
+  std::stable_sort(b.cams.begin(), b.cams.end(), [](const BracketedImage& x, const BracketedImage& y) { return x.ref_timestamp < y.ref_timestamp; });
+  return b;
+}
+
 }  // namespace mvba_host
