@@ -105,6 +105,31 @@ inline Bracketing lookup_images_and_brackets(double bracket_len, double timestam
   return out;
 }
 
+// lookupImagesNoBrackets (dense_map_utils.cc:1664-1743), the --no_rig case: every image of every sensor is a camera of its own, beg = end =
+// its position in the sensor's list, no timestamp offset, no offset bounds.
+inline Bracketing lookup_images_no_brackets(const std::vector<std::vector<double>>& image_stamps, const std::vector<std::vector<double>>& cloud_stamps) {
+  const int T = (int)image_stamps.size();
+  Bracketing out;
+  out.min_timestamp_offset.assign(T, -1.0e+100);
+  out.max_timestamp_offset.assign(T, 1.0e+100);
+  std::vector<int> image_start(T, 0), cloud_start(T, 0);
+  for (int t = 0; t < T; t++)
+    for (int k = 0; k < (int)image_stamps[t].size(); k++) {
+      BracketedImage cam;
+      cam.sensor = t; cam.timestamp = image_stamps[t][k]; cam.ref_timestamp = cam.timestamp; cam.beg_ref_index = k; cam.end_ref_index = k;
+      double found = -1.0;
+      if (!lookup_time(cam.timestamp, image_stamps[t], image_start[t], found) || found != cam.timestamp)
+        throw std::runtime_error("Cannot look up camera at time " + std::to_string(cam.timestamp) + ".");
+      cam.image_index = image_start[t];
+      if (!cloud_stamps.empty()) {
+        const bool ok = lookup_time(cam.timestamp, cloud_stamps[t], cloud_start[t], cam.cloud_timestamp);
+        cam.cloud_index = ok ? cloud_start[t] : -1;
+      }
+      out.cams.push_back(cam);
+    }
+  return out;
+}
+
 // lookupImages (dense_map_utils.cc:1745-1805) for the rig case: brackets, at least one image per sensor, cameras in order of their
 // reference-clock time (the reference calls std::sort there; a stable sort is used so that equal times keep the bracket order).
 inline Bracketing lookup_images(double bracket_len, double timestamp_offsets_max_change, const std::vector<double>& ref_timestamps,

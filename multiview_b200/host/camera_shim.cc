@@ -112,4 +112,18 @@ int mvh_lookup_images_and_brackets(double bracket_len, double max_change, int nu
     return (int)b.cams.size();
   } catch (const std::exception& e) { g_cam_err = e.what(); return -1; }
 }
+// lookup_images_no_brackets: outputs sized for the total number of images; returns the number of cameras, -1 on error
+int mvh_lookup_images_no_brackets(int num_sensors, const int* counts, const double* stamps, int* sensor, int* beg, int* end, double* timestamp, int* image_index) {
+  try {
+    std::vector<std::vector<double>> img(num_sensors);
+    size_t o = 0;
+    for (int t = 0; t < num_sensors; t++) { img[t].assign(stamps + o, stamps + o + counts[t]); o += counts[t]; }
+    mvba_host::Bracketing b = mvba_host::lookup_images_no_brackets(img, {});
+    for (size_t i = 0; i < b.cams.size(); i++) {
+      sensor[i] = b.cams[i].sensor; beg[i] = b.cams[i].beg_ref_index; end[i] = b.cams[i].end_ref_index; timestamp[i] = b.cams[i].timestamp;
+      image_index[i] = b.cams[i].image_index;
+    }
+    return (int)b.cams.size();
+  } catch (const std::exception& e) { g_cam_err = e.what(); return -1; }
+}
 }

@@ -103,3 +103,21 @@ def test_random_timelines_match_brute_force(host, seed):
         assert lo[t] >= offsets[t] - 0.03 and hi[t] <= offsets[t] + 0.03
         if sel:   # every kept image stays inside its bracket for any offset in the allowed range
             assert all(ref[c[1]] <= c[3] - hi[t] + 1e-4 and c[3] - lo[t] <= ref[c[2]] + 1e-4 for c in sel if c[1] != c[2])
+
+
+def test_no_rig_lookup_takes_every_image(host):
+    """lookupImagesNoBrackets: one camera per image, sensor-major, beg = end = position in the sensor's list; repeated timestamps are a
+    look-up failure exactly as in the reference (the forward scan stops on the first of the two)."""
+    stamps = [[1.0, 2.0, 3.5], [1.2, 2.2], [0.5]]
+    counts = np.array([3, 2, 1], np.int32); flat = np.concatenate(stamps)
+    n = 6
+    sensor = np.zeros(n, np.int32); beg = np.zeros(n, np.int32); end = np.zeros(n, np.int32); ts = np.zeros(n); img = np.zeros(n, np.int32)
+    args = lambda f: (3, counts.ctypes.data_as(ip), f.ctypes.data_as(dp), sensor.ctypes.data_as(ip), beg.ctypes.data_as(ip), end.ctypes.data_as(ip),
+                      ts.ctypes.data_as(dp), img.ctypes.data_as(ip))
+    assert host.mvh_lookup_images_no_brackets(*args(flat)) == 6
+    assert list(sensor) == [0, 0, 0, 1, 1, 2] and list(beg) == [0, 1, 2, 0, 1, 0] and list(end) == list(beg) and list(img) == list(beg)
+    assert list(ts) == [1.0, 2.0, 3.5, 1.2, 2.2, 0.5]
+    dup = flat.copy(); dup[1] = 1.0
+    assert host.mvh_lookup_images_no_brackets(*args(dup)) == 6 and list(img[:3]) == [0, 0, 2]   # equal stamps: the forward scan stops on the first of the two
+    bad = flat.copy(); bad[1] = 0.5                                      # a stamp the forward scan has already passed cannot be looked up
+    assert host.mvh_lookup_images_no_brackets(*args(bad)) == -1
