@@ -291,6 +291,9 @@ int mvba_upload(mvba_problem* h);
 int mvba_bench_jacobian(mvba_problem* h, int32_t repeats, float* ms_total);
 /* One fused normal-equation build (Jacobian + J'J + Schur elimination); milliseconds. */
 int mvba_bench_build(mvba_problem* h, int32_t repeats, float* ms_total);
+/* Host wall clock of the one-time structure analysis behind the first evaluate / solve of a pass: the problem assembly
+ * (what the AddResidualBlock loop of rig_calibrator.cc:1611-1903 costs the reference) and the reduced-system / tile tables. */
+int mvba_host_seconds(mvba_problem* h, double* seconds_setup, double* seconds_prepare);
 
 /* ---- multi-GPU: landmark sharding (each rank holds its own tracks; cameras replicated) ---- */
 /* nccl_unique_id: 128 bytes from ncclGetUniqueId on rank 0 (see mvba_nccl_unique_id). */

@@ -96,6 +96,7 @@ struct mvba_problem {
   int sm_count = 148;
   mvba::Solver* solver = nullptr;
   int64_t launches = 0;
+  double seconds_setup = 0, seconds_prepare = 0;  // host wall clock of setup() and solver_prepare() (one-time structure analysis)
   // multi-GPU
   void* nccl_comm = nullptr;
   int rank = 0, nranks = 1;

@@ -36,7 +36,11 @@ static int ready(mvba_problem* h) {
     cudaDeviceProp p; MVBA_CUDA(cudaGetDeviceProperties(&p, h->device));
     h->sm_count = p.multiProcessorCount;
   }
-  return setup(h);
+  if (h->built) return MVBA_OK;
+  auto t0 = std::chrono::steady_clock::now();
+  int rc2 = setup(h);
+  h->seconds_setup = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  return rc2;
 }
 
 }  // namespace mvba
@@ -257,7 +261,16 @@ int mvba_solve_options_init(mvba_solve_options* o) {
 int mvba_solve(mvba_problem* h, const mvba_solve_options* o, mvba_summary* s, mvba_iteration* its, int32_t max_its) {
   int rc = ready(h); if (rc) return rc;
   if (!o || !s) return fail(MVBA_EINVAL, "mvba_solve: null argument");
+  if (o->linear_solver != 0) return fail(MVBA_EINVAL, "mvba_solve: linear_solver must be 0 (PCG on the reduced camera system)");
+  if (o->preconditioner < 0 || o->preconditioner > 2) return fail(MVBA_EINVAL, "mvba_solve: preconditioner must be 0, 1 or 2");
   return solver_solve(h, *o, s, its, max_its);
+}
+
+int mvba_host_seconds(mvba_problem* h, double* seconds_setup, double* seconds_prepare) {
+  if (!h) return fail(MVBA_EINVAL, "mvba_host_seconds: null handle");
+  if (seconds_setup) *seconds_setup = h->seconds_setup;
+  if (seconds_prepare) *seconds_prepare = h->seconds_prepare;
+  return MVBA_OK;
 }
 
 int mvba_bench_build(mvba_problem* h, int32_t repeats, float* ms_total) {

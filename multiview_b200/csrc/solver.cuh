@@ -122,6 +122,10 @@ inline void solver_destroy(mvba_problem* h) {
 // Structure analysis: which pose-block pairs are co-observed by some track, shared-memory sizing.
 inline int solver_prepare(mvba_problem* h, bool with_F) {
   if (h->solver && h->solver->with_F == with_F) return MVBA_OK;
+  struct PrepTimer {
+    mvba_problem* h; std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+    ~PrepTimer() { h->seconds_prepare = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); }
+  } prep_timer{h};
   solver_destroy(h);
   Solver* s = new Solver();
   h->solver = s;
