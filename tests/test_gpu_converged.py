@@ -1,0 +1,56 @@
+"""GPU parity, part 3: the CONVERGED state of the device LM solve against the CPU oracle.
+
+north_star: "the converged cost must match to 1e-6 relative and the optimised poses to 1e-6 m and 1e-6 rad".  That is only
+well defined where the minimum is: the three hard families of test_gpu_parity_solve.py (depth + mesh with depth_to_image and
+scale floating; every intrinsic floating on ragged tracks; floating time offsets) are run here in a WELL-POSED form --
+the stay-near-initial landmark prior of the reference (XYZError with --tri_weight, rig_calibrator.cc:1886-1901) pins the
+7-dof gauge, there are no gross outliers, max_trust_region_radius = 1e7 keeps the LM damping from vanishing along the
+quaternion-norm null directions (the reference has no manifold, dense_map_utils.cc:171-178) -- and both sides iterate with
+an almost exact Newton step (eta = 1e-8) for 60 iterations, by which point the cost moves by less than 1e-8 relative per
+iteration.  tests/test_oracle_converged.py (CPU) shows that this state is path independent at the tolerances used here:
+the oracle on 1 and on 8 threads (different summation orders, different CG iteration counts) agree to 5e-7 in the poses
+(typically 1e-9) and to 5e-5 px in the intrinsics.
+
+Tolerances: cost 1e-6 relative (north_star); poses, rig transforms, depth transforms 1e-6 m / 1e-6 rad, landmarks 1e-6 m,
+time offsets 1e-6 s (north_star); focal length / optical centre / distortion coefficients 1e-4 in their native units
+(pixels, dimensionless) -- the oracle's own 1-vs-8-thread spread on them reaches 2e-5 px, far below the 0.5 px pixel noise."""
+import numpy as np
+import pytest
+
+from multiview_b200 import _abi, synth
+from test_gpu_parity_solve import CASES, _param_error
+
+pytestmark = pytest.mark.gpu
+
+FAMILIES = ("depth_mesh", "rig3_ragged_intr", "offsets")
+OPTS = dict(max_num_iterations=60, eta=1e-8, max_trust_region_radius=1e7)
+INTRINSIC = ("focal", "center", "distortion")
+
+
+def well_posed(name, seed=23):
+    kw = dict(CASES[name])
+    kw.update(tri_weight=5.0, tri_robust_threshold=1.0, outlier_frac=0.0)
+    return synth.make_problem(seed=seed, **kw)
+
+
+@pytest.mark.parametrize("name", FAMILIES)
+def test_converged_state_matches_the_oracle(name, oracle_lib, product_lib):
+    pr = well_posed(name)
+    snap = pr.snapshot()
+    o = _abi.Binding(oracle_lib, "oracle_", pr)
+    so, lo = o.solve(_abi.default_options(**OPTS), jac_mode=1, num_threads=1)
+    xo = pr.snapshot(); o.close()
+    pr.restore(snap)
+    g = _abi.Binding(product_lib, "mvba_", pr)
+    sg, lg = g.solve(_abi.default_options(**OPTS))
+    xg = pr.snapshot(); g.close()
+    # both sides are at a stationary point of the same objective: the last step no longer changes the cost
+    for s, log in ((so, lo), (sg, lg)):
+        assert abs(log[-1]["cost_change"]) <= 1e-7 * s.final_cost, log[-1]
+    assert abs(sg.initial_cost - so.initial_cost) <= 1e-9 * so.initial_cost
+    assert abs(sg.final_cost - so.final_cost) <= 1e-6 * so.final_cost
+    for k in xo:
+        if xo[k].size:
+            tol = 1e-4 if k in INTRINSIC else 1e-6
+            err = _param_error(k, xo[k], xg[k], pr)
+            assert err <= tol, (k, err)
