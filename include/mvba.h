@@ -44,7 +44,9 @@ enum {
   MVBA_ESTATE = -4,    /* call order violated (e.g. solve before observations were set)  */
   MVBA_EBRACKET = -5,  /* interpolation fraction outside [0,1]: rig_calibrator.cc:346    */
   MVBA_ENCCL = -6,     /* NCCL failure / NCCL not loadable                               */
-  MVBA_ENUMERIC = -7   /* non finite cost at the initial point                           */
+  MVBA_ENUMERIC = -7,  /* non finite cost at the initial point                           */
+  MVBA_EPEER = -8      /* multi-GPU: another rank failed before a collective (its own call
+                          returns the cause); every rank returns instead of blocking         */
 };
 
 /* Residual-block kinds, in the order the reference creates them for one track

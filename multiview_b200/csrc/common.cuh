@@ -35,6 +35,16 @@ static_assert(sizeof(CamTab) == 70 * 8, "CamTab layout");
 // coef' N (rotations of the bracketing poses, row 21) and coef' Nrc (rig rotation).
 struct CamCoef { double c[23][3]; };
 
+// Per-image data the tile kernel stages in shared memory (kernels_tile2.cuh; written by prep_cameras_kernel next to CamTab / CamCoef).
+struct alignas(16) CamPack {
+  double R[9], t[3];
+  double dl[3];      // t - t_rc: the rig rotation acts on Xc - t_rc = Z + dl
+  double c[23][3];   // CamCoef rows
+  int sensor, pad0;
+  double pad1;
+};
+static_assert(sizeof(CamPack) == 688 && sizeof(CamPack) % 16 == 0, "CamPack layout");
+
 // Per-sensor depth-to-image table (prep_sensors_kernel): Mc = s L m + td
 struct DepthTab {
   double L[9], td[3], s;

@@ -90,6 +90,7 @@ struct mvba_problem {
   mvba::DBuf<mvba::CamTab> d_tab;
   mvba::DBuf<mvba::DepthTab> d_dtab;
   mvba::DBuf<mvba::CamCoef> d_coef;
+  mvba::DBuf<mvba::CamPack> d_pack;   // allocated when the staged tile kernel is planned (solver.cuh), else null
   mvba::DBuf<double> d_scalars;   // small scratch of device scalars
   mvba::DBuf<int> d_err;
   mvba::DBuf<double> d_resid;     // residual rows scratch

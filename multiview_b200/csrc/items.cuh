@@ -46,7 +46,7 @@ __device__ __forceinline__ void load_camtab(const CamTab* __restrict__ tab, int 
   }
 }
 
-template <bool WANT_J>
+template <bool WANT_J, bool WANT_E = true>
 __device__ inline void eval_cam(const View& v, const double* __restrict__ x, const CamTab* __restrict__ tab, int64_t i,
                                 Item& it, double* Jd0, double* Jd1) {
   it.kind = MVBA_BLOCK_CAM; it.nr = 2;
@@ -59,7 +59,7 @@ __device__ inline void eval_cam(const View& v, const double* __restrict__ x, con
   }
   project_distort<WANT_J>(v.sens[it.sensor], x, it.Xc, v.pix[i], it.r, it.A, it.Jf, &it.Jc, Jd0, Jd1);
   it.r[2] = 0;
-  if (WANT_J) {
+  if (WANT_J && WANT_E) {
     double rt[10];  // R again (L1 hit) rather than 9 registers held across the projection
     {
       const double2* q = reinterpret_cast<const double2*>(tab + it.cid);

@@ -7,7 +7,8 @@ namespace mvba {
 
 // One thread per camera image (+ one per sensor for the depth tables).
 __global__ void prep_cameras_kernel(View v, const double* __restrict__ x, CamTab* __restrict__ tab,
-                                    DepthTab* __restrict__ dtab, int* __restrict__ err, CamCoef* __restrict__ coef) {
+                                    DepthTab* __restrict__ dtab, int* __restrict__ err, CamCoef* __restrict__ coef,
+                                    CamPack* __restrict__ pack) {
   int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c < v.C) {
     CamTab o;
@@ -24,6 +25,13 @@ __global__ void prep_cameras_kernel(View v, const double* __restrict__ x, CamTab
       for (int j = 0; j < 4; j++)
         for (int a = 0; a < 3; a++) { q.c[3 + j][a] = o.W0[4 * a + j]; q.c[10 + j][a] = o.W1[4 * a + j]; q.c[17 + j][a] = o.Wrc[4 * a + j]; }
       for (int a = 0; a < 3; a++) { q.c[21][a] = o.dalpha * o.wa[a]; q.c[22][a] = o.dalpha * o.dt[a]; }
+      if (pack) {
+        CamPack& k = pack[c];
+        for (int i = 0; i < 9; i++) k.R[i] = o.R[i];
+        for (int a = 0; a < 3; a++) { k.t[a] = o.t[a]; k.dl[a] = o.t[a] - o.trc[a]; }
+        for (int r = 0; r < 23; r++) for (int a = 0; a < 3; a++) k.c[r][a] = q.c[r][a];
+        k.sensor = v.cam_sensor[c]; k.pad0 = 0; k.pad1 = 0;
+      }
     }
     if (!ok) atomicExch(err, MVBA_EBRACKET);
   } else if (c < v.C + v.T && dtab != nullptr) {

@@ -16,10 +16,21 @@ static inline int rpc_degree_of(int num_dist) {  // rpc_distortion.cc:43-45
 }
 
 int allreduce_flags(mvba_problem* h, std::vector<uint8_t>& flags);  // solver.cuh: element-wise OR across ranks
+int rank_agree(mvba_problem* h, int rc);                               // solver.cuh: collective agreement on a return code
+// Scope guard for a function with rank-local early returns ahead of a collective: pass() is the agreement point on the
+// normal path; leaving the scope without it (an early `return fail(...)`) reports the failure to the waiting peers.
+struct AgreePoint {
+  mvba_problem* h; bool passed = false;
+  explicit AgreePoint(mvba_problem* hh) : h(hh) {}
+  int pass() { passed = true; return rank_agree(h, MVBA_OK); }
+  ~AgreePoint() { if (!passed) rank_agree(h, MVBA_EINVAL); }
+};
+
 void solver_destroy(mvba_problem* h);                                  // solver.cuh
 
 inline int setup(mvba_problem* h) {
   if (h->built) return MVBA_OK;
+  AgreePoint agree_layout(h);  // rank-local validation failures below must not leave the peers alone in the collective
   solver_destroy(h);  // structure tables of an earlier layout
   if (!h->have_params || !h->have_cams || !h->have_obs)
     return fail(MVBA_ESTATE, "mvba: set_params, set_cameras and set_observations must precede evaluation");
@@ -120,6 +131,8 @@ inline int setup(mvba_problem* h) {
 
   // Multi-rank: the column layout must be the same on every rank, so "used by at least one residual" means used on ANY rank
   // (a landmark shard that never sees an image would otherwise drop that image's pose block and shift every later column).
+  { int rc = agree_layout.pass(); if (rc) return rc; }
+  AgreePoint agree_end(h);
   if (h->nranks > 1) {
     std::vector<uint8_t> flags;
     flags.insert(flags.end(), pose_used.begin(), pose_used.end());
@@ -224,7 +237,7 @@ inline int setup(mvba_problem* h) {
   if (v.nx > 0 && cudaHostRegister(h->h_x.data(), sizeof(double) * v.nx, cudaHostRegisterDefault) == cudaSuccess) h->h_x_pinned = true;
   else cudaGetLastError();
   h->built = true;
-  return MVBA_OK;
+  return agree_end.pass();
 }
 
 // Caller arrays -> staging -> device parameter vector.
@@ -307,7 +320,7 @@ inline int check_device_error(mvba_problem* h) {
 inline int run_prep(mvba_problem* h, const double* x) {
   const View& v = h->view;
   int n = v.C + v.T;
-  prep_cameras_kernel<<<(n + 127) / 128, 128, 0, h->stream>>>(v, x, h->d_tab.p, h->d_dtab.p, h->d_err.p, h->d_coef.p);
+  prep_cameras_kernel<<<(n + 127) / 128, 128, 0, h->stream>>>(v, x, h->d_tab.p, h->d_dtab.p, h->d_err.p, h->d_coef.p, h->d_pack.p);
   h->launches++;
   return MVBA_OK;
 }

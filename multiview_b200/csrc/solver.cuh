@@ -11,20 +11,22 @@
 #include "handle.cuh"
 #include "kernels_lm.cuh"
 #include "kernels_camera.cuh"
+#include "kernels_camq.cuh"
 #include "kernels_tile.cuh"
+#include "kernels_tile2.cuh"
 
 namespace mvba {
 
 // ---- NCCL, loaded at run time so that libmvba.so has no link-time dependency on it ----
+struct NcclId { char b[128]; };
 struct Nccl {
   void* lib = nullptr;
   int (*GetUniqueId)(void*) = nullptr;
-  int (*CommInitRank)(void**, int, uint8_t[128], int) = nullptr;  // ncclUniqueId is passed by value (128 bytes)
+  int (*CommInitRank)(void**, int, NcclId, int) = nullptr;  // ncclUniqueId is passed BY VALUE (a 128-byte struct)
   int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
   int (*CommDestroy)(void*) = nullptr;
   const char* (*GetErrorString)(int) = nullptr;
 };
-struct NcclId { char b[128]; };
 inline Nccl& nccl() {
   static Nccl n;
   if (!n.lib) {
@@ -32,7 +34,7 @@ inline Nccl& nccl() {
     if (!n.lib) n.lib = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
     if (n.lib) {
       n.GetUniqueId = (int (*)(void*))dlsym(n.lib, "ncclGetUniqueId");
-      n.CommInitRank = (int (*)(void**, int, uint8_t[128], int))dlsym(n.lib, "ncclCommInitRank");
+      n.CommInitRank = (int (*)(void**, int, NcclId, int))dlsym(n.lib, "ncclCommInitRank");
       n.AllReduce = (int (*)(const void*, void*, size_t, int, int, void*, cudaStream_t))dlsym(n.lib, "ncclAllReduce");
       n.CommDestroy = (int (*)(void*))dlsym(n.lib, "ncclCommDestroy");
       n.GetErrorString = (const char* (*)(int))dlsym(n.lib, "ncclGetErrorString");
@@ -50,9 +52,8 @@ inline int comm_init(mvba_problem* h, int rank, int nranks, const uint8_t* id128
   if (nranks <= 1) { h->rank = 0; h->nranks = 1; return MVBA_OK; }
   Nccl& n = nccl();
   if (!n.lib || !n.CommInitRank) return fail(MVBA_ENCCL, "mvba: libnccl.so.2 not loadable");
-  typedef int (*init_t)(void**, int, NcclId, int);
   NcclId id; std::memcpy(id.b, id128, 128);
-  int rc = ((init_t)dlsym(n.lib, "ncclCommInitRank"))(&h->nccl_comm, nranks, id, rank);
+  int rc = n.CommInitRank(&h->nccl_comm, nranks, id, rank);
   if (rc) return fail(MVBA_ENCCL, std::string("ncclCommInitRank: ") + n.GetErrorString(rc));
   h->rank = rank; h->nranks = nranks;
   h->built = false;  // the column layout becomes the union over ranks (setup.cuh)
@@ -66,6 +67,21 @@ inline int allreduce(mvba_problem* h, void* buf, size_t n, int dtype, int op) {
   return rc ? fail(MVBA_ENCCL, std::string("ncclAllReduce: ") + nc.GetErrorString(rc)) : MVBA_OK;
 }
 
+// Collective agreement on a return code: every rank passes its own; when any rank failed, the healthy ranks get MVBA_EPEER
+// and return too instead of blocking in the next collective (the failing rank keeps its own code and message).
+inline int rank_agree(mvba_problem* h, int rc) {
+  if (h->nranks <= 1) return rc;
+  int32_t flag = rc != 0, any = 0;
+  DBuf<int32_t> d;
+  if (d.alloc(1) != cudaSuccess) return rc ? rc : fail(MVBA_ECUDA, "mvba: rank_agree allocation failed");
+  cudaMemcpyAsync(d.p, &flag, sizeof(flag), cudaMemcpyHostToDevice, h->stream);
+  const int arc = allreduce(h, d.p, 1, 2, 2);  // ncclInt32, ncclMax
+  cudaMemcpyAsync(&any, d.p, sizeof(any), cudaMemcpyDeviceToHost, h->stream);
+  cudaStreamSynchronize(h->stream);
+  if (rc) return rc;
+  if (arc) return arc;
+  return any ? fail(MVBA_EPEER, "mvba: another rank failed before a collective; see that rank's error") : MVBA_OK;
+}
 // Element-wise OR of a byte table across ranks (ncclUint8 = 1, ncclMax = 2): layout decisions every rank must share.
 inline int allreduce_flags(mvba_problem* h, std::vector<uint8_t>& flags) {
   if (h->nranks <= 1 || flags.empty()) return MVBA_OK;
@@ -102,12 +118,22 @@ struct Solver {
   DBuf<int32_t> citems, chunk_cam, chunk_beg;
   int nchunks = 0, cam_batch = 0, cam_ldj = 0, grid_cam = 1;
   size_t smem_cam = 0;
+  // pass A without free intrinsics / depth columns: per-image 6 x 6 accumulators (kernels_camq.cuh)
+  bool cam_fast = false;
+  DBuf<double> camQ;
+  int grid_camq = 1;
   // pass B fast path: tracks sorted by first pose block and cut into window tiles; the rest fall back
   // (static round tables: staged blocks, per-track slots, gather groups and their contributors, kernels_tile.cuh)
   DBuf<int32_t> tile_w0, tile_wn, tile_round0, round_trk0, round_blk0, round_grp0, fallback;
   DBuf<TBlk> t_blk; DBuf<TTrk> t_trk; DBuf<TGrp> t_grp; DBuf<uint16_t> t_con;
   int ntiles = 0, nrounds = 0, nfallback = 0, tile_nt = 512, tile_pr = 4, tile_K = 1, tile_icap = 64, tile_nx = 0, tile_L8max = 8, grid_tile = 1;
   size_t smem_tile = 0;
+  // pass B, staged variant (kernels_tile2.cuh): per-round blobs fetched by bulk copy, two CTAs per SM
+  bool any_x = false, tile2 = false;
+  DBuf<int32_t> t2_c0, t2_nc, t2_rounds, tile_ctr;
+  DBuf<int64_t> t2_blob0; DBuf<uint32_t> t2_bytes0; DBuf<uint8_t> t2_blob;
+  int t2_K = 1, t2_icap = 32, t2_ccap = 0, t2_L8max = 8, t2_blob_cap = 64, t2_maxs = 8, grid_tile2 = 1;
+  size_t smem_tile2 = 0;
   Reduced R{};
   Bsr A{};
 };
@@ -127,6 +153,7 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
     ~PrepTimer() { h->seconds_prepare = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); }
   } prep_timer{h};
   solver_destroy(h);
+  AgreePoint agree_pattern(h);  // rank-local failures below must not leave the peers alone in the collective
   Solver* s = new Solver();
   h->solver = s;
   const View& v = h->view;
@@ -165,6 +192,8 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
     trk_any[p] = items > 0; trk_items[p] = items;
   }
   for (int u = 0; u < nb; u++) flag[(size_t)u * nb + u] = 1;  // diagonal always present (damping)
+  { int rc = agree_pattern.pass(); if (rc) return rc; }
+  AgreePoint agree_end(h);
   { int rc = allreduce_flags(h, flag); if (rc) return rc; }      // block pattern of S = union over the ranks' landmark shards
   std::vector<int32_t> pairtab((size_t)nb * nb, -1), row_ptr(nb + 1, 0), col, slot;
   int64_t ns = 0;
@@ -286,11 +315,36 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
     MVBA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_cam, camera_pass_kernel, MVBA_CAM_THREADS, s->smem_cam));
     s->grid_cam = std::max(1, std::min(s->nchunks, h->sm_count * std::max(occ_cam, 1)));
   }
+  {  // pass A, images whose f columns are all pose / rig / offset columns: 27 accumulators per image instead of staged rows
+    bool any_x = false;
+    for (int t = 0; t < v.T; t++) {
+      const SensorDev& sd = v.sens[t];
+      any_x = any_x || sd.c_focal >= 0 || sd.c_center >= 0 || sd.c_dist >= 0 || sd.c_d2i >= 0 || sd.c_scale >= 0;
+    }
+    s->any_x = any_x;
+    const char* ev = std::getenv("MVBA_CAM_STAGED");  // developer switch: force the staged-row kernel
+    s->cam_fast = !any_x && !(ev && ev[0] == '1');
+    if (s->cam_fast) {
+      MVBA_CUDA(s->camQ.alloc((size_t)std::max(v.C, 1) * MVBA_CAMQ_N));
+      int occ_q = 1;
+      MVBA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_q, camq_kernel, 256, 0));
+      s->grid_camq = std::max(1, std::min(s->nchunks, h->sm_count * std::max(occ_q, 1)));
+    }
+  }
   {  // ---- pass B fast path: window tiles ----
     // 16 warps x <= 16 accumulator blocks of 8x8 cover the upper block triangle up to L8 = 176 local columns
     int maxspan = 0;
     for (int p = 0; p < v.P; p++) if (trk_any[p]) maxspan = std::max(maxspan, (int)trk_span[p]);
-    const int capw = (176 - s->B) / 7;
+    // staged kernel (tile2): 8 warps x <= 16 accumulator blocks cover L8 = 120 local columns including the v row
+    bool use_t2 = !s->any_x && v.C < (1 << 24);
+    { const char* ev = std::getenv("MVBA_TILE_UNSTAGED"); if (ev && ev[0] == '1') use_t2 = false; }  // developer switch
+    const int capw2 = (119 - s->B) / 7;
+    if (use_t2) {  // nearly every track must fit its window, otherwise the wider windows of the unstaged kernel win
+      int64_t wide = 0, any = 0;
+      for (int p = 0; p < v.P; p++) if (trk_any[p]) { any++; wide += (trk_span[p] > capw2 || trk_items[p] > 32); }
+      if (s->B > 119 || capw2 < 1 || wide * 100 > any) use_t2 = false;
+    }
+    const int capw = use_t2 ? capw2 : (176 - s->B) / 7;
     int W = std::min(maxspan + 2, capw);
     if (s->B > 176 || W < 0) W = -1;  // nothing fits: every track takes the generic kernel
     std::vector<int32_t> order, fb;
@@ -300,7 +354,7 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
     // at least ~6 tiles per CTA so that the static tile -> CTA assignment balances (small shards of a multi-GPU run)
     int tile_div = 6;  // tiles per SM (tuning knob: MVBA_TILE_DIV)
     if (const char* ev = std::getenv("MVBA_TILE_DIV")) { const int d = std::atoi(ev); if (d >= 1 && d <= 64) tile_div = d; }
-    const int tile_max = (int)std::max<size_t>(48, std::min<size_t>(512, order.size() / (size_t)(tile_div * std::max(h->sm_count, 1))));
+    const int tile_max = (int)std::max<size_t>(48, std::min<size_t>(512, order.size() / (size_t)(tile_div * (use_t2 ? 2 : 1) * std::max(h->sm_count, 1))));
     size_t i = 0;
     int wn_max = 0;
     while (i < order.size()) {
@@ -329,10 +383,47 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
       nx = std::max(nx, (sd.c_d2i >= 0 ? v.nd2i : 0) + (sd.c_scale >= 0));
     }
     s->tile_nx = nx;
-    {
+    double mean_items = 1.0;
+    { double tot = 0; for (int p : order) tot += trk_items[p]; if (!order.empty()) mean_items = std::max(1.0, tot / order.size()); }
+    // image range of every tile (the staged kernel copies the window's CamPack rows to shared memory in one piece)
+    std::vector<int32_t> tc0(s->ntiles, 0), tnc(s->ntiles, 0);
+    if (use_t2) {
+      int maxnc = 0;
+      for (int t = 0; t < s->ntiles; t++) {
+        int lo = INT32_MAX, hi = -1;
+        for (int ti = t0[t]; ti < t0[t + 1]; ti++) {
+          const int p = order[ti];
+          auto see = [&](int64_t obs) { const int c = h->ocid[obs]; lo = std::min(lo, c); hi = std::max(hi, c); };
+          for (int64_t i = h->h_trk_obs0[p]; i < h->h_trk_obs0[p + 1]; i++) see(i);
+          for (int64_t j = h->h_trk_dtri0[p]; j < h->h_trk_dtri0[p + 1]; j++) see(h->h_dtri_obs[j]);
+          for (int64_t j = h->h_trk_dmesh0[p]; j < h->h_trk_dmesh0[p + 1]; j++) see(h->h_dmesh_obs[j]);
+        }
+        if (hi >= 0) { tc0[t] = lo; tnc[t] = hi - lo + 1; maxnc = std::max(maxnc, tnc[t]); }
+      }
+      // two CTAs per SM: half of the SM's shared memory each
+      int sm_smem = 0;
+      MVBA_CUDA(cudaDeviceGetAttribute(&sm_smem, cudaDevAttrMaxSharedMemoryPerMultiprocessor, h->device));
+      const size_t budget = std::min<size_t>((size_t)dev_smem, ((size_t)sm_smem - 2 * 1024) / 2);
+      s->t2_L8max = std::max(8, (7 * wn_max + s->B + 1 + 7) & ~7);
+      s->t2_ccap = std::min(maxnc, 40);
+      int K = 32, icap = 0, bcap = 0;
+      for (; K >= 1; K--) {
+        icap = (int)std::min<double>((double)MVBA_T2_THREADS, std::max(32.0, std::ceil(1.15 * mean_items * K)));
+        bcap = (int)t2_blob_bytes(K, K, icap, MVBA_T2_GCAP);
+        if (tile2_smem(K, icap, s->t2_ccap, s->t2_L8max, bcap) <= budget) break;
+      }
+      if (K < 4) use_t2 = false;  // (the window cap above was the staged kernel's: still valid for the unstaged one)
+      else {
+        while (icap < MVBA_T2_THREADS && icap < 2 * mean_items * K &&
+               tile2_smem(K, icap + 1, s->t2_ccap, s->t2_L8max, (int)t2_blob_bytes(K, K, icap + 1, MVBA_T2_GCAP)) <= budget) icap++;
+        s->t2_K = K; s->t2_icap = icap; s->t2_blob_cap = (int)t2_blob_bytes(K, K, icap, MVBA_T2_GCAP);
+        for (int t = 0; t < s->ntiles; t++) tnc[t] = std::min(tnc[t], s->t2_ccap);
+      }
+    }
+    s->tile2 = use_t2;
+    if (use_t2) { s->tile_K = s->t2_K; s->tile_icap = s->t2_icap; }
+    else {
       // the largest K (tracks per round) whose staging fits, with room for ~1.15 x the mean number of blocks per track
-      double mean_items = 1.0;
-      { double tot = 0; for (int p : order) tot += trk_items[p]; if (!order.empty()) mean_items = std::max(1.0, tot / order.size()); }
       int K = 32, icap = 0;  // phase b3 maps the staged tracks to the lanes of a warp
       for (; K >= 1; K--) {
         icap = (int)std::min<double>(511.0, std::max(32.0, std::ceil(1.15 * mean_items * K)));
@@ -341,27 +432,53 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
       if (K < 1) return fail(MVBA_EINVAL, "mvba: tile staging does not fit shared memory");
       while (icap < 511 && tile_smem(K, icap + 1, nx, s->tile_L8max) + 1024 <= (size_t)dev_smem && icap < 2 * mean_items * K) icap++;
       s->tile_K = K; s->tile_icap = icap;
-    }
-    s->smem_tile = tile_smem(s->tile_K, s->tile_icap, nx, s->tile_L8max);
-    {  // accumulator blocks per warp: upper block triangle of the widest window over 16 warps
+      s->smem_tile = tile_smem(s->tile_K, s->tile_icap, nx, s->tile_L8max);
+      // accumulator blocks per warp: upper block triangle of the widest window over 16 warps
       const int nb8 = s->tile_L8max / 8, per = (nb8 * (nb8 + 1) / 2 + 15) / 16;
       s->tile_pr = per <= 4 ? 4 : per <= 8 ? 8 : 16;
+      if (s->tile_pr == 4) MVBA_CUDA(cudaFuncSetAttribute(tile_kernel<512, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_tile));
+      else if (s->tile_pr == 8) MVBA_CUDA(cudaFuncSetAttribute(tile_kernel<512, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_tile));
+      else MVBA_CUDA(cudaFuncSetAttribute(tile_kernel<512, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_tile));
     }
-    if (s->tile_pr == 4) MVBA_CUDA(cudaFuncSetAttribute(tile_kernel<512, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_tile));
-    else if (s->tile_pr == 8) MVBA_CUDA(cudaFuncSetAttribute(tile_kernel<512, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_tile));
-    else MVBA_CUDA(cudaFuncSetAttribute(tile_kernel<512, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_tile));
+    const int gcap = use_t2 ? MVBA_T2_GCAP : INT32_MAX;  // gather groups of one round
     // ---- static round tables ----
     std::vector<int32_t> tile_round0{0}, round_trk0{0}, round_blk0{0}, round_grp0{0};
     std::vector<TBlk> blk; std::vector<TTrk> ttrk; std::vector<TGrp> grp; std::vector<uint16_t> con;
     blk.reserve((size_t)(v.N + v.n_dtri + v.n_dmesh + v.n_prior)); ttrk.reserve(order.size());
     struct Key { int lcol; int single; std::vector<uint16_t> c; };
     std::vector<Key> keys;
+    std::vector<int> gkeys;
+    auto count_groups = [&](int p) -> int {  // distinct (pose block | rig transform | offset) blocks touched by the track's f blocks
+      gkeys.clear();
+      auto add = [&](int key) { if (std::find(gkeys.begin(), gkeys.end(), key) == gkeys.end()) gkeys.push_back(key); };
+      auto f_block = [&](int64_t obs) {
+        const int c = h->ocid[obs];
+        const SensorDev& sd = v.sens[h->cam_sensor[c]];
+        const int p0 = h->h_cam_p0[c], p1 = h->h_cam_p1[c];
+        const int cb = h->h_pose_col[p0], ce = p1 >= 0 ? h->h_pose_col[p1] : -1;
+        if (cb >= 0) add(cb);
+        if (ce >= 0) add(ce);
+        if (sd.c_rig >= 0) add(sd.c_rig);
+        if (sd.c_off >= 0) add(sd.c_off);
+      };
+      for (int64_t i = h->h_trk_obs0[p]; i < h->h_trk_obs0[p + 1]; i++) f_block(i);
+      for (int64_t j = h->h_trk_dtri0[p]; j < h->h_trk_dtri0[p + 1]; j++) f_block(h->h_dtri_obs[j]);
+      for (int64_t j = h->h_trk_dmesh0[p]; j < h->h_trk_dmesh0[p + 1]; j++) f_block(h->h_dmesh_obs[j]);
+      return (int)gkeys.size();
+    };
     for (int t = 0; t < s->ntiles; t++) {
       const int w0 = tw0[t], Wt = twn[t];
       int ti = t0[t];
       while (ti < t0[t + 1]) {
-        int kc = 0, nit = 0;
-        while (ti + kc < t0[t + 1] && kc < s->tile_K && nit + trk_items[order[ti + kc]] <= s->tile_icap) { nit += trk_items[order[ti + kc]]; kc++; }
+        int kc = 0, nit = 0, ng = 0;
+        while (ti + kc < t0[t + 1] && kc < s->tile_K && nit + trk_items[order[ti + kc]] <= s->tile_icap) {
+          if (use_t2) {  // one gather thread per group: count the track's distinct parameter blocks
+            const int n = count_groups(order[ti + kc]);
+            if (ng + n > gcap) break;
+            ng += n;
+          }
+          nit += trk_items[order[ti + kc]]; kc++;
+        }
         if (kc == 0) return fail(MVBA_EINVAL, "mvba: a tile track does not fit the staging buffer");
         int q = 0;
         for (int k = 0; k < kc; k++) {
@@ -408,10 +525,77 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
     if (grp.empty()) grp.push_back(TGrp{});
     if (blk.empty()) blk.push_back(TBlk{0, 0});
     if (ttrk.empty()) ttrk.push_back(TTrk{0, 0, 0});
-    MVBA_CUDA(s->tile_round0.upload(tile_round0)); MVBA_CUDA(s->round_trk0.upload(round_trk0)); MVBA_CUDA(s->round_blk0.upload(round_blk0));
-    MVBA_CUDA(s->round_grp0.upload(round_grp0)); MVBA_CUDA(s->t_blk.upload(blk)); MVBA_CUDA(s->t_trk.upload(ttrk)); MVBA_CUDA(s->t_grp.upload(grp));
     MVBA_CUDA(s->t_con.upload(con));
-    s->grid_tile = std::max(1, std::min(s->ntiles, h->sm_count));
+    if (!use_t2) {
+      MVBA_CUDA(s->tile_round0.upload(tile_round0)); MVBA_CUDA(s->round_trk0.upload(round_trk0)); MVBA_CUDA(s->round_blk0.upload(round_blk0));
+      MVBA_CUDA(s->round_grp0.upload(round_grp0)); MVBA_CUDA(s->t_blk.upload(blk)); MVBA_CUDA(s->t_trk.upload(ttrk)); MVBA_CUDA(s->t_grp.upload(grp));
+      s->grid_tile = std::max(1, std::min(s->ntiles, h->sm_count));
+    } else {
+      // ---- one contiguous blob per round: TRoundHdr | TTrk[kc] | next round's landmarks | TSlot[nit] | TGrp[ngrp] ----
+      auto rkc = [&](int r) { return round_trk0[r + 1] - round_trk0[r]; };
+      auto rbytes = [&](int r, bool last) {
+        return t2_blob_bytes(rkc(r), last ? 0 : rkc(r + 1), round_blk0[r + 1] - round_blk0[r], round_grp0[r + 1] - round_grp0[r]);
+      };
+      std::vector<int32_t> trounds(s->ntiles, 0);
+      std::vector<int64_t> tblob0(s->ntiles, 0);
+      std::vector<uint32_t> tbytes0(s->ntiles, 0);
+      size_t total = 0;
+      uint32_t maxbytes = 64;
+      for (int t = 0; t < s->ntiles; t++)
+        for (int r = tile_round0[t]; r < tile_round0[t + 1]; r++) { const uint32_t nb = rbytes(r, r + 1 == tile_round0[t + 1]); total += nb; maxbytes = std::max(maxbytes, nb); }
+      if ((size_t)maxbytes > (size_t)s->t2_blob_cap) return fail(MVBA_EINVAL, "mvba: round table larger than planned");
+      std::vector<uint8_t> blob(std::max<size_t>(total, 16), 0);
+      size_t off = 0;
+      for (int t = 0; t < s->ntiles; t++) {
+        trounds[t] = tile_round0[t + 1] - tile_round0[t];
+        tblob0[t] = (int64_t)off;
+        for (int r = tile_round0[t]; r < tile_round0[t + 1]; r++) {
+          const bool last = r + 1 == tile_round0[t + 1];
+          const int kc = rkc(r), kn = last ? 0 : rkc(r + 1), nit = round_blk0[r + 1] - round_blk0[r], ng = round_grp0[r + 1] - round_grp0[r];
+          const uint32_t nb = rbytes(r, last);
+          if (r == tile_round0[t]) tbytes0[t] = nb;
+          uint8_t* b = blob.data() + off;
+          TRoundHdr hd{};
+          hd.kc = kc; hd.nit = nit; hd.ngrp = ng; hd.kc_next = kn; hd.next_bytes = last ? 0 : rbytes(r + 1, r + 2 == tile_round0[t + 1]);
+          std::memcpy(b, &hd, sizeof(hd));
+          uint8_t* q = b + 32;
+          std::memcpy(q, ttrk.data() + round_trk0[r], (size_t)kc * sizeof(TTrk)); q += t2_align16(8u * kc);
+          for (int k = 0; k < kn; k++) { const int32_t pn = ttrk[round_trk0[r + 1] + k].p; std::memcpy(q + 4 * k, &pn, 4); }
+          q += t2_align16(4u * kn);
+          for (int k = 0; k < kc; k++) {
+            const TTrk& tk = ttrk[round_trk0[r] + k];
+            for (int i = 0; i < tk.n; i++) {
+              const TBlk& bk = blk[round_blk0[r] + tk.q0 + i];
+              TSlot sl{};
+              int cid = 0;
+              if (bk.kind == 0) { cid = h->ocid[bk.idx]; sl.a = h->opid[bk.idx]; sl.px = h->opix[2 * (size_t)bk.idx]; sl.py = h->opix[2 * (size_t)bk.idx + 1]; }
+              else { sl.a = bk.idx; if (bk.kind == 1) cid = h->ocid[h->h_dtri_obs[bk.idx]]; else if (bk.kind == 2) cid = h->ocid[h->h_dmesh_obs[bk.idx]]; }
+              sl.b = (uint32_t)cid | ((uint32_t)bk.kind << 24) | ((uint32_t)k << 27);
+              std::memcpy(q + 16 * (size_t)(tk.q0 + i), &sl, 16);
+            }
+          }
+          q += 16 * (size_t)nit;
+          std::memcpy(q, grp.data() + round_grp0[r], (size_t)ng * sizeof(TGrp));
+          off += nb;
+        }
+      }
+      MVBA_CUDA(s->t2_blob.upload(blob)); MVBA_CUDA(s->t2_blob0.upload(tblob0)); MVBA_CUDA(s->t2_bytes0.upload(tbytes0));
+      MVBA_CUDA(s->t2_rounds.upload(trounds)); MVBA_CUDA(s->t2_c0.upload(tc0)); MVBA_CUDA(s->t2_nc.upload(tnc));
+      MVBA_CUDA(s->tile_ctr.alloc(1));
+      MVBA_CUDA(h->d_pack.alloc(std::max(v.C, 1)));
+      s->smem_tile2 = tile2_smem(s->t2_K, s->t2_icap, s->t2_ccap, s->t2_L8max, s->t2_blob_cap);
+      const int nb8 = s->t2_L8max / 8, per = (nb8 * (nb8 + 1) / 2 + 7) / 8;
+      s->t2_maxs = per <= 8 ? 8 : 16;
+      int occ2 = 1;
+      if (s->t2_maxs == 8) {
+        MVBA_CUDA(cudaFuncSetAttribute(tile2_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_tile2));
+        MVBA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ2, tile2_kernel<8>, MVBA_T2_THREADS, s->smem_tile2));
+      } else {
+        MVBA_CUDA(cudaFuncSetAttribute(tile2_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_tile2));
+        MVBA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ2, tile2_kernel<16>, MVBA_T2_THREADS, s->smem_tile2));
+      }
+      s->grid_tile2 = std::max(1, std::min(s->ntiles, h->sm_count * std::max(occ2, 1)));
+    }
   }
   int occ = 1;
   MVBA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, build_kernel, 32 * s->wpb_build, s->smem_build));
@@ -427,7 +611,7 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
       s->pcg_coop_grid = std::max(1, std::min(want, std::min(occ_pcg, 2) * h->sm_count));
     }
   }
-  return MVBA_OK;
+  return agree_end.pass();
 }
 
 }  // namespace mvba

@@ -33,7 +33,17 @@ inline int run_build(mvba_problem* h, const mvba_solve_options& o, double radius
   a.mode = mode; a.maxposes = s->maxposes; a.maxdz = s->maxdz; a.vwmax = s->vwmax;
   a.trk_list = nullptr; a.ntrk = v.P;
   if (s->tm) s->tm->begin(9);
-  if (s->nchunks > 0 && s->nf > 0) {  // pass A: F'F, F'r, diag(F'F) by camera image
+  if (s->nchunks > 0 && s->nf > 0 && s->cam_fast) {  // pass A, pose-type columns only: per-image 6 x 6 accumulators, then T'QT
+    MVBA_CUDA(s->camQ.zero(h->stream));
+    CamQArgs qa{};
+    qa.x = h->d_x.p; qa.tab = h->d_tab.p; qa.dtab = h->d_dtab.p;
+    qa.chunk_cam = s->chunk_cam.p; qa.chunk_beg = s->chunk_beg.p; qa.citems = s->citems.p; qa.nchunks = s->nchunks; qa.Q = s->camQ.p;
+    camq_kernel<<<s->grid_camq, 256, 0, h->stream>>>(v, qa);
+    CamFoldArgs fa{};
+    fa.tab = h->d_tab.p; fa.coef = h->d_coef.p; fa.Q = s->camQ.p; fa.jscale_f = a.jscale_f; fa.mode = mode;
+    camfold_kernel<<<(v.C + 3) / 4, 128, 0, h->stream>>>(v, fa, s->R);
+    h->launches += 2;
+  } else if (s->nchunks > 0 && s->nf > 0) {  // pass A: F'F, F'r, diag(F'F) by camera image
     CamPassArgs ca{};
     ca.x = h->d_x.p; ca.tab = h->d_tab.p; ca.dtab = h->d_dtab.p; ca.jscale_f = a.jscale_f;
     ca.chunk_cam = s->chunk_cam.p; ca.chunk_beg = s->chunk_beg.p; ca.citems = s->citems.p; ca.nchunks = s->nchunks;
@@ -45,7 +55,17 @@ inline int run_build(mvba_problem* h, const mvba_solve_options& o, double radius
     build_kernel<<<s->grid_build, 32 * s->wpb_build, s->smem_build, h->stream>>>(v, a, s->R);
     h->launches++;
   } else if (v.P > 0) {  // pass B: landmark blocks, Schur elimination
-    if (s->ntiles > 0) {
+    if (s->ntiles > 0 && s->tile2) {  // staged variant: per-round blobs by bulk copy, two CTAs per SM, dynamic tile queue
+      MVBA_CUDA(cudaMemsetAsync(s->tile_ctr.p, 0, sizeof(int), h->stream));
+      Tile2Args ta{};
+      ta.b = a; ta.pack = h->d_pack.p; ta.tile_w0 = s->tile_w0.p; ta.tile_wn = s->tile_wn.p; ta.tile_c0 = s->t2_c0.p; ta.tile_nc = s->t2_nc.p;
+      ta.tile_rounds = s->t2_rounds.p; ta.tile_blob0 = s->t2_blob0.p; ta.tile_bytes0 = s->t2_bytes0.p; ta.blob = s->t2_blob.p; ta.con = s->t_con.p;
+      ta.tile_ctr = s->tile_ctr.p; ta.ntiles = s->ntiles; ta.K = s->t2_K; ta.icap = s->t2_icap; ta.ccap = s->t2_ccap; ta.L8max = s->t2_L8max;
+      ta.blob_cap = s->t2_blob_cap;
+      if (s->t2_maxs == 8) tile2_kernel<8><<<s->grid_tile2, MVBA_T2_THREADS, s->smem_tile2, h->stream>>>(v, ta, s->R);
+      else tile2_kernel<16><<<s->grid_tile2, MVBA_T2_THREADS, s->smem_tile2, h->stream>>>(v, ta, s->R);
+      h->launches++;
+    } else if (s->ntiles > 0) {
       TileArgs ta{};
       ta.b = a; ta.tile_w0 = s->tile_w0.p; ta.tile_wn = s->tile_wn.p; ta.tile_round0 = s->tile_round0.p;
       ta.round_trk0 = s->round_trk0.p; ta.round_blk0 = s->round_blk0.p; ta.round_grp0 = s->round_grp0.p;
@@ -65,7 +85,18 @@ inline int run_build(mvba_problem* h, const mvba_solve_options& o, double radius
   }
   if (s->tm) s->tm->end();
 #ifdef MVBA_TILE_PROFILE
-  if (mode == 0 && s->ntiles > 0) {
+  if (mode == 0 && s->ntiles > 0 && s->tile2) {
+    unsigned long long pr[8], z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    cudaStreamSynchronize(h->stream);
+    cudaMemcpyFromSymbol(pr, g_tile_prof, sizeof(pr));
+    cudaMemcpyToSymbol(g_tile_prof, z, sizeof(z));
+    double tot = 0; for (int i = 0; i < 8; i++) tot += (double)pr[i];
+    std::printf("tile2 prof (thread 0 of each CTA, %% of cycles): prologue+flush %.1f | P1 %.1f | bar %.1f | P2 (inverse, warp 0) %.1f | bar %.1f | scale+bar %.1f | P3 %.1f | bar %.1f  (Mcycles/CTA %.2f)\n",
+                100 * pr[0] / tot, 100 * pr[1] / tot, 100 * pr[2] / tot, 100 * pr[3] / tot, 100 * pr[4] / tot, 100 * pr[5] / tot, 100 * pr[6] / tot, 100 * pr[7] / tot,
+                tot / s->grid_tile2 * 1e-6);
+    static bool once2 = false;
+    if (!once2) { once2 = true; std::printf("tile2 plan: K %d icap %d ccap %d L8max %d blob_cap %d maxs %d ntiles %d nrounds %d nfallback %d grid %d smem %zu B %d\n", s->t2_K, s->t2_icap, s->t2_ccap, s->t2_L8max, s->t2_blob_cap, s->t2_maxs, s->ntiles, s->nrounds, s->nfallback, s->grid_tile2, s->smem_tile2, s->B); }
+  } else if (mode == 0 && s->ntiles > 0) {
     unsigned long long pr[8], z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     cudaStreamSynchronize(h->stream);
     cudaMemcpyFromSymbol(pr, g_tile_prof, sizeof(pr));
@@ -155,7 +186,7 @@ inline int solver_solve(mvba_problem* h, const mvba_solve_options& o, mvba_summa
   auto t0 = std::chrono::steady_clock::now();
   std::memset(S, 0, sizeof(*S));
   const int64_t launches0 = h->launches;
-  int rc = solver_prepare(h, o.preconditioner == 0); if (rc) return rc;
+  int rc = solver_prepare(h, o.preconditioner == 0); if (rc) { solver_destroy(h); return rc; }
   Solver* s = h->solver;
   const View& v = h->view;
   rc = upload_params(h); if (rc) return rc;

@@ -189,6 +189,21 @@ class Problem:
         for k, v in self.param_arrays().items():
             v[...] = snap[k]
 
+    def keep_observations(self, keep: np.ndarray) -> "Problem":
+        """Copy of the problem with only the observations where `keep` is true (tracks, cameras and parameters unchanged)."""
+        import copy
+        keep = np.asarray(keep, bool)
+        q = copy.copy(self)
+        q.pid = self.pid[keep].copy(); q.cid = self.cid[keep].copy()
+        q.pix = self.pix.reshape(-1, 2)[keep].reshape(-1).copy()
+        for nm, w in (("has_depth", 1), ("depth_xyz", 3), ("has_mesh", 1), ("mesh_xyz", 3)):
+            a = getattr(self, nm)
+            setattr(q, nm, None if a is None else a.reshape(-1, w)[keep].reshape(-1).copy())
+        for nm in ("world_to_ref", "ref_to_cam", "offsets", "focal", "center", "distortion", "depth_to_image",
+                   "depth_scale", "world_to_cam", "xyz"):
+            setattr(q, nm, getattr(self, nm).copy())
+        return q
+
     def shard(self, rank: int, world: int, locality: bool = True) -> "Problem":
         """Landmark shard for rank `rank` of `world`: ranges of tracks balanced by observation count; cameras and all
         non-landmark parameters are replicated.  With `locality` the tracks are first ordered by the
@@ -307,6 +322,22 @@ def default_sensors(kind: str):
         und = co.copy()
         return [Sensor("rpc_cam", w, h, 900.0, (cx, cy), np.concatenate([co, und]))]
     raise ValueError(kind)
+
+
+def reference_offset_bounds(ref_stamps, cam_sensor, cam_beg, cam_end, cam_stamp, offsets, max_change=1.0):
+    """Bounds the reference puts on a floated ref_to_sensor_timestamp_offset (dense_map_utils.cc:1607-1652, applied at
+    rig_calibrator.cc:1742-1745): every image must stay inside its bracket, the offset may move by at most
+    --timestamp_offsets_max_change, and both ends are pulled in by 1e-5."""
+    T = len(offsets)
+    lo = np.full(T, -1.0e100); hi = np.full(T, 1.0e100)
+    for t in range(T):
+        sel = (cam_sensor == t) & (cam_beg != cam_end)
+        if sel.any():
+            lo[t] = max(lo[t], float(np.max(cam_stamp[sel] - ref_stamps[cam_end[sel]])))
+            hi[t] = min(hi[t], float(np.min(cam_stamp[sel] - ref_stamps[cam_beg[sel]])))
+    lo = np.maximum(lo, offsets - max_change) + 1.0e-5
+    hi = np.minimum(hi, offsets + max_change) - 1.0e-5
+    return lo, hi
 
 
 def make_problem(*, seed=1, sensors="pinhole", num_ref=50, num_landmarks=10000, obs_per_track=4,
@@ -486,6 +517,7 @@ def make_problem(*, seed=1, sensors="pinhole", num_ref=50, num_landmarks=10000, 
     if tri_weight > 0:
         priors[BLOCK_TRI] = (np.arange(P, dtype=np.int32), xyz0.reshape(-1).copy(), float(tri_weight), float(tri_robust_threshold))
 
+    off_lo, off_hi = reference_offset_bounds(ref_stamps, cam_sensor, cam_beg, cam_end, cam_stamp, offsets0)
     pm = np.zeros(T, np.uint8)
     if float_poses:
         pm[:] = 1 if no_rig else 0
@@ -498,7 +530,7 @@ def make_problem(*, seed=1, sensors="pinhole", num_ref=50, num_landmarks=10000, 
         d2im[min(1, T - 1)] = 1
     pr = Problem(S, bool(no_rig), bool(affine_depth), float(robust_threshold), float(depth_tri_weight), float(depth_mesh_weight),
                  np.ascontiguousarray(w2r0.reshape(-1)), ref_stamps, np.ascontiguousarray(r2c0.reshape(-1)), offsets0,
-                 offsets0 - 1.0, offsets0 + 1.0, focal0, center0, dist0, np.ascontiguousarray(d2i0.reshape(-1)), scale0,
+                 off_lo, off_hi, focal0, center0, dist0, np.ascontiguousarray(d2i0.reshape(-1)), scale0,
                  world_to_cam0, np.ascontiguousarray(xyz0.reshape(-1)),
                  cam_sensor.astype(np.int32), cam_beg.astype(np.int32), cam_end.astype(np.int32), cam_stamp.astype(np.float64),
                  pid.astype(np.int32), cid.astype(np.int32), pix32, has_depth, depth_xyz, has_mesh, mesh_xyz, priors,
