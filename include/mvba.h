@@ -296,6 +296,12 @@ int mvba_bench_build(mvba_problem* h, int32_t repeats, float* ms_total);
 /* Host wall clock of the one-time structure analysis behind the first evaluate / solve of a pass: the problem assembly
  * (what the AddResidualBlock loop of rig_calibrator.cc:1611-1903 costs the reference) and the reduced-system / tile tables. */
 int mvba_host_seconds(mvba_problem* h, double* seconds_setup, double* seconds_prepare);
+/* Which kernels the last mvba_solve planned for the normal-equation build (diagnostic; the tests use it to make sure a case
+ * really runs the path it is meant to cover).  plan[0] pass A: 1 = per-image 6x6 accumulators, 0 = staged rows;
+ * plan[1] pass B: 2 = staged window tiles (bulk-copied round tables), 1 = window tiles, 0 = none; plan[2] accumulator blocks
+ * per warp of the tile kernel; plan[3] tracks per round; plan[4] tiles; plan[5] rounds; plan[6] tracks taking the generic
+ * warp-per-track kernel; plan[7] padded local width of the widest window.  MVBA_ESTATE before the first solve. */
+int mvba_build_plan(mvba_problem* h, int32_t plan[8]);
 
 /* ---- multi-GPU: landmark sharding (each rank holds its own tracks; cameras replicated) ---- */
 /* nccl_unique_id: 128 bytes from ncclGetUniqueId on rank 0 (see mvba_nccl_unique_id). */

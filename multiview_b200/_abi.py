@@ -215,6 +215,13 @@ class Binding:
                                            _p(xyz, c_double_p), _p(mean, c_double_p)))
         return has, xyz.reshape(-1, 3), mean.reshape(-1, 3)
 
+    def build_plan(self):
+        """mvba_build_plan of the last solve as a dict (product library only)."""
+        plan = (C.c_int32 * 8)()
+        self._ck(self.lib.mvba_build_plan(self.h, plan))
+        keys = ("pass_a_accumulators", "pass_b", "blocks_per_warp", "tracks_per_round", "tiles", "rounds", "fallback_tracks", "l8max")
+        return dict(zip(keys, list(plan)))
+
     def solve(self, options: SolveOptions | None = None, max_log=256, jac_mode=1, num_threads=0):
         o = options or default_options()
         s = Summary()

@@ -192,7 +192,7 @@ __device__ inline void prep_depth(const View& v, const double* __restrict__ x, i
 template <bool WANT_J>
 __device__ __forceinline__ void project_distort(const SensorDev& s, const double* __restrict__ x, const double* Xc,
                                                 float2 meas, double* r, double* A, double* Jf, double* Jc,
-                                                double* Jd0, double* Jd1) {
+                                                double* Jd0, double* Jd1, const double* __restrict__ fov) {
   const double f = x[s.x_focal];
   const double cx = x[s.x_center], cy = x[s.x_center + 1];
   const double iz = 1.0 / Xc[2];
@@ -211,10 +211,10 @@ __device__ __forceinline__ void project_distort(const SensorDev& s, const double
     const double ux = f * px, uy = f * py;
     const double nx = ux / f, ny = uy / f;
     const double ru = sqrt(nx * nx + ny * ny);
-    const double th = tan(0.5 * w);
-    const double k = 2.0 * th;
+    const double k = fov[0];             // 2 tan(w / 2), once per sensor and evaluation point (prep_cameras_kernel)
+    const double th = 0.5 * k;
     const double at = atan(ru * k);
-    const double rd = at * (1.0 / w);
+    const double rd = at * fov[1];       // 1 / w
     double conv = 1.0;
     if (ru > 1e-5) conv = rd / ru;
     dx = (cx - hx) + conv * (nx * f) + hx; dy = (cy - hy) + conv * (ny * f) + hy;

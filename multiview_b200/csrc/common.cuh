@@ -77,6 +77,7 @@ struct View {
   const int32_t *cam_sensor, *cam_p0, *cam_p1;  // p0/p1: pose block index (p1 = -1: identity_vec)
   const double *cam_bs, *cam_es, *cam_cs;
   const int32_t* pose_col;  // npose: first reduced column or -1
+  double* fov_tab;          // 2 per sensor, written by prep_cameras_kernel: 2 tan(w/2) and 1/w of a fisheye (FOV) sensor
   // observations (track-major, reference order)
   const int32_t *pid, *cid;
   const float2* pix;
@@ -134,6 +135,12 @@ __device__ __forceinline__ void cauchy(double a, double s, double* half_rho, dou
   double sum = 1.0 + s / b;
   *half_rho = 0.5 * b * log(sum);
   *sqrt_rho1 = sqrt(1.0 / sum);
+}
+
+// Corrector scale alone (the build needs the cost itself only at the first point of a solve: no logarithm otherwise).
+__device__ __forceinline__ double cauchy_sr(double a, double s) {
+  double b = a * a;
+  return sqrt(1.0 / (1.0 + s / b));
 }
 
 }  // namespace mvba

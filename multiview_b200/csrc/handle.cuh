@@ -89,6 +89,7 @@ struct mvba_problem {
   mvba::DBuf<double> d_x, d_xnew;
   mvba::DBuf<mvba::CamTab> d_tab;
   mvba::DBuf<mvba::DepthTab> d_dtab;
+  mvba::DBuf<double> d_fov;
   mvba::DBuf<mvba::CamCoef> d_coef;
   mvba::DBuf<mvba::CamPack> d_pack;   // allocated when the staged tile kernel is planned (solver.cuh), else null
   mvba::DBuf<double> d_scalars;   // small scratch of device scalars

@@ -57,7 +57,7 @@ __device__ inline void eval_cam(const View& v, const double* __restrict__ x, con
     double rt[12];
     load_camtab(tab, it.cid, Xw, it.Xc, it.Z, rt);
   }
-  project_distort<WANT_J>(v.sens[it.sensor], x, it.Xc, v.pix[i], it.r, it.A, it.Jf, &it.Jc, Jd0, Jd1);
+  project_distort<WANT_J>(v.sens[it.sensor], x, it.Xc, v.pix[i], it.r, it.A, it.Jf, &it.Jc, Jd0, Jd1, v.fov_tab + 2 * it.sensor);
   it.r[2] = 0;
   if (WANT_J && WANT_E) {
     double rt[10];  // R again (L1 hit) rather than 9 registers held across the projection

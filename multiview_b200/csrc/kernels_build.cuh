@@ -35,6 +35,7 @@ struct BuildArgs {
   double* diagE;  // 3 per landmark: diag(E'E) (COLNORM mode)
   double* cost;   // sum of 0.5 rho
   int mode;       // 0 full build, 1 column norms only
+  int want_cost;  // accumulate sum 0.5 rho (only the first build of a solve needs it: later costs come from the candidate pass)
   int maxposes;   // per-track capacity of the local pose list
   int maxdz;      // max nd_nz
   int vwmax;      // max virtual width

@@ -31,7 +31,7 @@ struct CamQArgs {
   double* Q;                   // C x MVBA_CAMQ_N, zeroed before the launch
 };
 
-__global__ void __launch_bounds__(256) camq_kernel(View v, CamQArgs a) {
+__global__ void __launch_bounds__(256, 2) camq_kernel(View v, CamQArgs a) {
   __shared__ double red[8][MVBA_CAMQ_N];
   const int tid = threadIdx.x, lane = tid & 31, wib = tid >> 5;
   for (int ch = blockIdx.x; ch < a.nchunks; ch += gridDim.x) {

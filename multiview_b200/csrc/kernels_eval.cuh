@@ -34,10 +34,18 @@ __global__ void prep_cameras_kernel(View v, const double* __restrict__ x, CamTab
       }
     }
     if (!ok) atomicExch(err, MVBA_EBRACKET);
-  } else if (c < v.C + v.T && dtab != nullptr) {
-    DepthTab d;
-    prep_depth(v, x, c - v.C, d);
-    dtab[c - v.C] = d;
+  } else if (c < v.C + v.T) {
+    const int t = c - v.C;
+    if (dtab != nullptr) {
+      DepthTab d;
+      prep_depth(v, x, t, d);
+      dtab[t] = d;
+    }
+    if (v.sens[t].nd == 1) {  // FOV model constants of this evaluation point (camera_params.cc:269-281)
+      const double w = x[v.sens[t].x_dist];
+      v.fov_tab[2 * t] = 2.0 * tan(0.5 * w);
+      v.fov_tab[2 * t + 1] = 1.0 / w;
+    }
   }
 }
 

@@ -93,8 +93,9 @@ __device__ __forceinline__ double tile_eval(const View& v, const BuildArgs& a, c
   const int p = it.pid;
   double s = it.r[0] * it.r[0] + it.r[1] * it.r[1];
   if (it.nr == 3) s += it.r[2] * it.r[2];
-  double hr, sr;
-  cauchy(it.loss_a, s, &hr, &sr);
+  double hr = 0, sr;
+  if (a.want_cost) cauchy(it.loss_a, s, &hr, &sr);
+  else sr = cauchy_sr(it.loss_a, s);
   double se[3] = {1, 1, 1};
   if (a.jscale_e) { se[0] = a.jscale_e[3 * (size_t)p]; se[1] = a.jscale_e[3 * (size_t)p + 1]; se[2] = a.jscale_e[3 * (size_t)p + 2]; }
   double Es[9];

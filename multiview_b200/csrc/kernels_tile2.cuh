@@ -9,9 +9,10 @@
 //     1-D bulk copy (cp.async.bulk -> mbarrier) issued a phase earlier, the window's per-image data (CamPack: R, t,
 //     t - t_rc, the 23 coefficient rows, sensor) by one bulk copy per tile, and the next round's landmark coordinates
 //     by cp.async while the current round is gathered.  No dependent global load is left in the evaluation;
-//   * Hinv = L L' (3 x 3 Cholesky) is folded into the gathered rows, Gs = G L, so ONE staged matrix feeds both DMMA
-//     operands (C += Gs Gs'), the Y = G Hinv phase and its buffer are gone, and the reduced right-hand side comes out
-//     of the same GEMM through one extra row  v = L' E'r  (its column of C is  Gs v = G Hinv E'r);
+//   * the landmark block is factored, E'E + D = R'R, and U = R^-1 (so Hinv = U U') is folded into the gathered rows,
+//     Gs = G U: ONE staged matrix feeds both DMMA operands (C += Gs Gs'), the Y = G Hinv phase and its buffer are gone,
+//     and the reduced right-hand side comes out of the same GEMM through one extra row  v = U' E'r  (its column of C
+//     is  Gs v = G Hinv E'r);
 //   * one thread gathers a whole (track, parameter block) group (7 rows x 3): the block's M = (sr A)'E and
 //     N = [Z]x M are loaded once per contributor instead of once per row;
 //   * tiles are handed out by an atomic counter (no static tile -> CTA map, so small multi-GPU shards balance).
@@ -37,8 +38,10 @@ __host__ __device__ inline uint32_t t2_blob_bytes(int kc, int kc_next, int nit, 
   return 32u + t2_align16(8u * kc) + t2_align16(4u * kc_next) + 16u * nit + 16u * ngrp;
 }
 
-struct TRec2 { double M[9], Z[3], y[3], H[6], g[3]; };
-static_assert(sizeof(TRec2) == 192, "TRec2 layout");
+// 25 doubles: an ODD stride in 8-byte units, so that the same field of consecutive slots falls in different banks
+// (a 24-double record puts every slot in one of two bank groups: 16-way conflicts on each access)
+struct TRec2 { double M[9], Z[3], y[3], H[6], g[3], pad; };
+static_assert(sizeof(TRec2) == 200, "TRec2 layout");
 
 struct Tile2Args {
   BuildArgs b;
@@ -57,12 +60,14 @@ struct Tile2Args {
   int K, icap, ccap, L8max, blob_cap;
 };
 
-// Shared memory (bytes): Gs[L8max][KK] | rec[icap] | Xs[2][K][6] | Ls[K][6] | cs[L8max] | pack[ccap] | blob | rcid[icap] | mbarriers
+// Shared memory: Gs[L8max][KK] | pack[ccap] | blob | Xs[2][K][6] | Ls[K][6] | cs[L8max] | rec[icap] | rcid[icap] | mbarriers
+// (the bulk-copy destinations first: they need 16-byte alignment)
 __host__ __device__ inline size_t tile2_smem(int K, int icap, int ccap, int L8max, int blob_cap) {
   const size_t KK = tile_kk(K);
-  size_t n = ((size_t)L8max * KK + (size_t)2 * K * 6 + (size_t)K * 6 + (size_t)L8max) * 8;
-  n += (size_t)icap * sizeof(TRec2) + (size_t)ccap * sizeof(CamPack) + (size_t)blob_cap;
-  n += (((size_t)icap * 4 + 15) & ~(size_t)15) + 32;
+  size_t n = (size_t)L8max * KK * 8 + (size_t)ccap * sizeof(CamPack) + (size_t)blob_cap;
+  n += ((size_t)2 * K * 6 + (size_t)K * 6 + (size_t)L8max) * 8;
+  n += (size_t)icap * sizeof(TRec2);
+  n += (((size_t)icap * 4 + 7) & ~(size_t)7) + 16;
   return n + 16;
 }
 
@@ -114,14 +119,14 @@ __global__ void __launch_bounds__(MVBA_T2_THREADS, 2) tile2_kernel(View v, Tile2
   const int tid = threadIdx.x, lane = tid & 31, wib = tid >> 5;
   const int K = a.K, KK = tile_kk(K);
   double* Gs = reinterpret_cast<double*>(smem_raw);
-  TRec2* rec = reinterpret_cast<TRec2*>(Gs + (size_t)a.L8max * KK);
-  double* Xs = reinterpret_cast<double*>(rec + a.icap);
+  CamPack* pack_s = reinterpret_cast<CamPack*>(Gs + (size_t)a.L8max * KK);
+  unsigned char* blob_s = reinterpret_cast<unsigned char*>(pack_s + a.ccap);
+  double* Xs = reinterpret_cast<double*>(blob_s + a.blob_cap);
   double* Ls = Xs + (size_t)2 * K * 6;
   double* cs = Ls + (size_t)K * 6;
-  CamPack* pack_s = reinterpret_cast<CamPack*>(cs + a.L8max);
-  unsigned char* blob_s = reinterpret_cast<unsigned char*>(pack_s + a.ccap);
-  int* rcid = reinterpret_cast<int*>(blob_s + a.blob_cap);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<unsigned char*>(rcid) + (((size_t)a.icap * 4 + 15) & ~(size_t)15));
+  TRec2* rec = reinterpret_cast<TRec2*>(cs + a.L8max);
+  int* rcid = reinterpret_cast<int*>(rec + a.icap);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<unsigned char*>(rcid) + (((size_t)a.icap * 4 + 7) & ~(size_t)7));
   uint64_t* bar_blob = bars;
   uint64_t* bar_pack = bars + 1;
   __shared__ int s_tile;
@@ -212,7 +217,7 @@ __global__ void __launch_bounds__(MVBA_T2_THREADS, 2) tile2_kernel(View v, Tile2
             it.Xc[i] = it.Z[i] + cp->t[i];
             yv[i] = it.Z[i] + cp->dl[i];
           }
-          project_distort<true>(v.sens[cp->sensor], a.b.x, it.Xc, make_float2(sl.px, sl.py), it.r, it.A, it.Jf, &it.Jc, nullptr, nullptr);
+          project_distort<true>(v.sens[cp->sensor], a.b.x, it.Xc, make_float2(sl.px, sl.py), it.r, it.A, it.Jf, &it.Jc, nullptr, nullptr, v.fov_tab + 2 * cp->sensor);
           it.r[2] = 0;
 #pragma unroll
           for (int i = 0; i < 2; i++)
@@ -228,8 +233,9 @@ __global__ void __launch_bounds__(MVBA_T2_THREADS, 2) tile2_kernel(View v, Tile2
         }
         double s = it.r[0] * it.r[0] + it.r[1] * it.r[1];
         if (it.nr == 3) s += it.r[2] * it.r[2];
-        double hr, sr;
-        cauchy(it.loss_a, s, &hr, &sr);
+        double hr = 0, sr;
+        if (a.b.want_cost) cauchy(it.loss_a, s, &hr, &sr);
+        else sr = cauchy_sr(it.loss_a, s);
         cost_acc += hr;
         const double se[3] = {Xk[3], Xk[4], Xk[5]};
         double Es[9];
@@ -279,27 +285,31 @@ __global__ void __launch_bounds__(MVBA_T2_THREADS, 2) tile2_kernel(View v, Tile2
 #pragma unroll
             for (int k = 0; k < 3; k++) gE[k] += r.g[k];
           }
-          H[0] += fmin(fmax(H[0], a.b.min_diag), a.b.max_diag) / a.b.radius;
-          H[3] += fmin(fmax(H[3], a.b.min_diag), a.b.max_diag) / a.b.radius;
-          H[5] += fmin(fmax(H[5], a.b.min_diag), a.b.max_diag) / a.b.radius;
-          double Hi[6];
-          inv_sym3(H, Hi);
+          const double ir = 1.0 / a.b.radius;  // warp-uniform
+          H[0] += fmin(fmax(H[0], a.b.min_diag), a.b.max_diag) * ir;
+          H[3] += fmin(fmax(H[3], a.b.min_diag), a.b.max_diag) * ir;
+          H[5] += fmin(fmax(H[5], a.b.min_diag), a.b.max_diag) * ir;
+          // H = R'R (R upper triangular) with reciprocal square roots, U = R^-1:  Hinv = U U'  and  G Hinv G' = (G U)(G U)'
+          const double i00 = rsqrt(H[0]);
+          const double r01 = H[1] * i00, r02 = H[2] * i00;
+          const double i11 = rsqrt(H[3] - r01 * r01);
+          const double r12 = (H[4] - r01 * r02) * i11;
+          const double i22 = rsqrt(H[5] - r02 * r02 - r12 * r12);
+          const double u01 = -r01 * i00 * i11, u12 = -r12 * i11 * i22;
+          const double u02 = -(r02 * i00 + r12 * u01) * i22;
+          double Hi[6];  // xx xy xz yy yz zz
+          Hi[0] = i00 * i00 + u01 * u01 + u02 * u02; Hi[1] = u01 * i11 + u02 * u12; Hi[2] = u02 * i22;
+          Hi[3] = i11 * i11 + u12 * u12; Hi[4] = u12 * i22; Hi[5] = i22 * i22;
 #pragma unroll
           for (int k = 0; k < 6; k++) a.b.Hinv[6 * (size_t)tk.p + k] = Hi[k];
 #pragma unroll
           for (int k = 0; k < 3; k++) a.b.ge[3 * (size_t)tk.p + k] = gE[k];
-          // Hinv = L L', L lower triangular: l00 l10 l11 l20 l21 l22
-          const double l00 = sqrt(Hi[0]);
-          const double l10 = Hi[1] / l00, l20 = Hi[2] / l00;
-          const double l11 = sqrt(Hi[3] - l10 * l10);
-          const double l21 = (Hi[4] - l20 * l10) / l11;
-          const double l22 = sqrt(Hi[5] - l20 * l20 - l21 * l21);
           double* L = Ls + 6 * tid;
-          L[0] = l00; L[1] = l10; L[2] = l11; L[3] = l20; L[4] = l21; L[5] = l22;
-          double* vr = Gs + (size_t)Lt * KK + 3 * tid;  // v = L' E'r
-          vr[0] = l00 * gE[0] + l10 * gE[1] + l20 * gE[2];
-          vr[1] = l11 * gE[1] + l21 * gE[2];
-          vr[2] = l22 * gE[2];
+          L[0] = i00; L[1] = u01; L[2] = i11; L[3] = u02; L[4] = u12; L[5] = i22;
+          double* vr = Gs + (size_t)Lt * KK + 3 * tid;  // v = U' E'r
+          vr[0] = i00 * gE[0];
+          vr[1] = u01 * gE[0] + i11 * gE[1];
+          vr[2] = u02 * gE[0] + u12 * gE[1] + i22 * gE[2];
         }
         if (tid < kc_next) t2_fetch_landmark(v, a.b, next_p[tid], Xnext + 6 * tid);
       } else if (tid - 32 < ngrp) {
@@ -365,18 +375,18 @@ __global__ void __launch_bounds__(MVBA_T2_THREADS, 2) tile2_kernel(View v, Tile2
       T2PROF(3);
       __syncthreads();
       T2PROF(4);
-      // ---- Gs = diag(cs) G L, in place (every group owns its 7 x 3 entries) ----
+      // ---- Gs = diag(cs) G U, in place (every group owns its 7 x 3 entries) ----
       if (g_rows > 0) {
         const double* L = Ls + 6 * g_k;
-        const double l00 = L[0], l10 = L[1], l11 = L[2], l20 = L[3], l21 = L[4], l22 = L[5];
+        const double u00 = L[0], u01 = L[1], u11 = L[2], u02 = L[3], u12 = L[4], u22 = L[5];
 #pragma unroll
         for (int r = 0; r < 7; r++) {
           if (r < g_rows) {
             double* gp = Gs + (size_t)(g_lcol + r) * KK + 3 * g_k;
             const double o0 = gp[0], o1 = gp[1], o2 = gp[2];
-            gp[0] = o0 * l00 + o1 * l10 + o2 * l20;
-            gp[1] = o1 * l11 + o2 * l21;
-            gp[2] = o2 * l22;
+            gp[0] = o0 * u00;
+            gp[1] = o0 * u01 + o1 * u11;
+            gp[2] = o0 * u02 + o1 * u12 + o2 * u22;
           }
         }
       }
@@ -388,22 +398,26 @@ __global__ void __launch_bounds__(MVBA_T2_THREADS, 2) tile2_kernel(View v, Tile2
         boff += bbytes; bbytes = hd.next_bytes;
         if (tid == 0) { mbar_expect_tx(bar_blob, bbytes); bulk_g2s(blob_s, a.blob + boff, bbytes, bar_blob); }
       }
-      // ---- P3: C += Gs Gs' on the FP64 tensor cores, K dimension = 3 kc ----
-      if (ns > 0) {
+      // ---- P3: C += Gs Gs' on the FP64 tensor cores, K dimension = 3 kc.  The row offsets of every block's two fragments
+      //      are fixed for the tile: the inner loop is two shared loads and one DMMA per block, nothing else (slots past
+      //      the warp's last block repeat block 0 into accumulators that are never flushed) ----
+      {
         const int kend = (3 * kc + 3) & ~3;
         const double* base = Gs + (size_t)gid * KK + tig;
-#pragma unroll(MAXS <= 8 ? 2 : 1)
-        for (int k0 = 0; k0 < kend; k0 += 4) {
+        int offa[MAXS], offb[MAXS];
+        {
           int bi = bi0, bj = bj0;
-          double av = base[(size_t)(8 * bi) * KK + k0];
 #pragma unroll
           for (int sl = 0; sl < MAXS; sl++) {
-            if (sl < ns) {
-              const double bv = bj == bi ? av : base[(size_t)(8 * bj) * KK + k0];
-              dmma884(acc[sl][0], acc[sl][1], av, bv);
-              if (++bj == nb8) { bi++; bj = bi; if (sl + 1 < ns) av = base[(size_t)(8 * bi) * KK + k0]; }
-            }
+            if (sl < ns) { offa[sl] = 8 * bi * KK; offb[sl] = 8 * bj * KK; if (++bj == nb8) { bi++; bj = bi; } }
+            else { offa[sl] = 0; offb[sl] = 0; }
           }
+        }
+#pragma unroll 2
+        for (int k0 = 0; k0 < kend; k0 += 4) {
+          const double* kb = base + k0;
+#pragma unroll
+          for (int sl = 0; sl < MAXS; sl++) dmma884(acc[sl][0], acc[sl][1], kb[offa[sl]], kb[offb[sl]]);
         }
       }
       T2PROF(6);

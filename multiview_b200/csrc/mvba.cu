@@ -273,6 +273,18 @@ int mvba_host_seconds(mvba_problem* h, double* seconds_setup, double* seconds_pr
   return MVBA_OK;
 }
 
+int mvba_build_plan(mvba_problem* h, int32_t plan[8]) {
+  if (!h || !plan) return fail(MVBA_EINVAL, "mvba_build_plan: null argument");
+  if (!h->solver) return fail(MVBA_ESTATE, "mvba_build_plan: no solve has been planned on this handle");
+  const Solver* s = h->solver;
+  plan[0] = s->cam_fast ? 1 : 0;
+  plan[1] = s->ntiles == 0 ? 0 : s->tile2 ? 2 : 1;
+  plan[2] = s->tile2 ? s->t2_maxs : s->tile_pr;
+  plan[3] = s->tile_K; plan[4] = s->ntiles; plan[5] = s->nrounds; plan[6] = s->nfallback;
+  plan[7] = s->tile2 ? s->t2_L8max : s->tile_L8max;
+  return MVBA_OK;
+}
+
 int mvba_bench_build(mvba_problem* h, int32_t repeats, float* ms_total) {
   int rc = ready(h); if (rc) return rc;
   return solver_bench_build(h, repeats, ms_total);

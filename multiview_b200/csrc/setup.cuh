@@ -223,6 +223,7 @@ inline int setup(mvba_problem* h) {
   MVBA_CUDA(h->d_trk_pm0.upload(h->h_trk_pm0)); MVBA_CUDA(h->d_trk_pt0.upload(h->h_trk_pt0));
   MVBA_CUDA(h->d_x.alloc(v.nx)); MVBA_CUDA(h->d_xnew.alloc(v.nx));
   MVBA_CUDA(h->d_tab.alloc(C)); MVBA_CUDA(h->d_dtab.alloc(T)); MVBA_CUDA(h->d_coef.alloc(C));
+  MVBA_CUDA(h->d_fov.alloc(2 * (size_t)T)); v.fov_tab = h->d_fov.p;
   MVBA_CUDA(h->d_scalars.alloc(64)); MVBA_CUDA(h->d_err.alloc(1));
   v.cam_sensor = h->d_cam_sensor.p; v.cam_p0 = h->d_cam_p0.p; v.cam_p1 = h->d_cam_p1.p;
   v.cam_bs = h->d_cam_bs.p; v.cam_es = h->d_cam_es.p; v.cam_cs = h->d_cam_cs.p; v.pose_col = h->d_pose_col.p;

@@ -349,12 +349,16 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
     if (s->B > 176 || W < 0) W = -1;  // nothing fits: every track takes the generic kernel
     std::vector<int32_t> order, fb;
     for (int p = 0; p < v.P; p++) if (trk_any[p]) { if (W >= 0 && trk_span[p] <= W && trk_items[p] <= 32) order.push_back(p); else fb.push_back(p); }
-    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return trk_umin[a] < trk_umin[b]; });
+    // by first pose block, then by span: tracks of one tile then need the same window, and narrow tracks get narrow windows
+    // (the dense window update costs (7 Wt + B)^2 per track whatever the track touches)
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return trk_umin[a] != trk_umin[b] ? trk_umin[a] < trk_umin[b] : trk_span[a] < trk_span[b]; });
     std::vector<int32_t> t0, tw0, twn;
     // at least ~6 tiles per CTA so that the static tile -> CTA assignment balances (small shards of a multi-GPU run)
     int tile_div = 6;  // tiles per SM (tuning knob: MVBA_TILE_DIV)
     if (const char* ev = std::getenv("MVBA_TILE_DIV")) { const int d = std::atoi(ev); if (d >= 1 && d <= 64) tile_div = d; }
     const int tile_max = (int)std::max<size_t>(48, std::min<size_t>(512, order.size() / (size_t)(tile_div * (use_t2 ? 2 : 1) * std::max(h->sm_count, 1))));
+    int tile_min = std::min(tile_max, 128);  // tracks a tile must hold before a window growth may close it (MVBA_TILE_MIN)
+    if (const char* ev = std::getenv("MVBA_TILE_MIN")) { const int d = std::atoi(ev); if (d >= 1) tile_min = std::min(tile_max, d); }
     size_t i = 0;
     int wn_max = 0;
     while (i < order.size()) {
@@ -364,6 +368,7 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
       while (j < order.size() && (int)(j - i) < tile_max) {
         int p = order[j], e = trk_umin[p] + trk_span[p];
         if (trk_span[p] > 0 && e - w0 > W) break;
+        if (trk_span[p] > 0 && e > hi && hi > w0 && (int)(j - i) >= tile_min) break;  // a wider track starts the next tile
         if (trk_span[p] > 0) hi = std::max(hi, e);
         j++;
       }
@@ -409,13 +414,14 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
       int K = 32, icap = 0, bcap = 0;
       for (; K >= 1; K--) {
         icap = (int)std::min<double>((double)MVBA_T2_THREADS, std::max(32.0, std::ceil(1.15 * mean_items * K)));
+        icap = std::min(MVBA_T2_THREADS, (icap + 1) & ~1);
         bcap = (int)t2_blob_bytes(K, K, icap, MVBA_T2_GCAP);
         if (tile2_smem(K, icap, s->t2_ccap, s->t2_L8max, bcap) <= budget) break;
       }
       if (K < 4) use_t2 = false;  // (the window cap above was the staged kernel's: still valid for the unstaged one)
       else {
-        while (icap < MVBA_T2_THREADS && icap < 2 * mean_items * K &&
-               tile2_smem(K, icap + 1, s->t2_ccap, s->t2_L8max, (int)t2_blob_bytes(K, K, icap + 1, MVBA_T2_GCAP)) <= budget) icap++;
+        while (icap + 2 <= MVBA_T2_THREADS && icap < 2 * mean_items * K &&
+               tile2_smem(K, icap + 2, s->t2_ccap, s->t2_L8max, (int)t2_blob_bytes(K, K, icap + 2, MVBA_T2_GCAP)) <= budget) icap += 2;
         s->t2_K = K; s->t2_icap = icap; s->t2_blob_cap = (int)t2_blob_bytes(K, K, icap, MVBA_T2_GCAP);
         for (int t = 0; t < s->ntiles; t++) tnc[t] = std::min(tnc[t], s->t2_ccap);
       }
@@ -585,15 +591,16 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
       MVBA_CUDA(h->d_pack.alloc(std::max(v.C, 1)));
       s->smem_tile2 = tile2_smem(s->t2_K, s->t2_icap, s->t2_ccap, s->t2_L8max, s->t2_blob_cap);
       const int nb8 = s->t2_L8max / 8, per = (nb8 * (nb8 + 1) / 2 + 7) / 8;
-      s->t2_maxs = per <= 8 ? 8 : 16;
+      s->t2_maxs = 16;
+      for (int m : {4, 5, 6, 7, 8, 10, 12, 16}) if (m >= per) { s->t2_maxs = m; break; }
       int occ2 = 1;
-      if (s->t2_maxs == 8) {
-        MVBA_CUDA(cudaFuncSetAttribute(tile2_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_tile2));
-        MVBA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ2, tile2_kernel<8>, MVBA_T2_THREADS, s->smem_tile2));
-      } else {
-        MVBA_CUDA(cudaFuncSetAttribute(tile2_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_tile2));
-        MVBA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ2, tile2_kernel<16>, MVBA_T2_THREADS, s->smem_tile2));
-      }
+#define MVBA_T2_PLAN(M)                                                                                                                   \
+  case M:                                                                                                                                 \
+    MVBA_CUDA(cudaFuncSetAttribute(tile2_kernel<M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_tile2));                      \
+    MVBA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ2, tile2_kernel<M>, MVBA_T2_THREADS, s->smem_tile2));                       \
+    break;
+      switch (s->t2_maxs) { MVBA_T2_PLAN(4) MVBA_T2_PLAN(5) MVBA_T2_PLAN(6) MVBA_T2_PLAN(7) MVBA_T2_PLAN(8) MVBA_T2_PLAN(10) MVBA_T2_PLAN(12) MVBA_T2_PLAN(16) }
+#undef MVBA_T2_PLAN
       s->grid_tile2 = std::max(1, std::min(s->ntiles, h->sm_count * std::max(occ2, 1)));
     }
   }

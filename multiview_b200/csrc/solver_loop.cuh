@@ -20,7 +20,7 @@ struct Timers {
 };
 
 // mode 0: full fused build at x for the given radius; mode 1: squared column norms only.
-inline int run_build(mvba_problem* h, const mvba_solve_options& o, double radius, int mode, bool scaled) {
+inline int run_build(mvba_problem* h, const mvba_solve_options& o, double radius, int mode, bool scaled, bool want_cost = true) {
   Solver* s = h->solver;
   const View& v = h->view;
   MVBA_CUDA(cudaMemsetAsync(s->red.p, 0, s->red_n * sizeof(double), h->stream));
@@ -30,7 +30,7 @@ inline int run_build(mvba_problem* h, const mvba_solve_options& o, double radius
   a.jscale_f = scaled ? s->jscale_f.p : nullptr; a.jscale_e = scaled ? s->jscale_e.p : nullptr;
   a.radius = radius; a.min_diag = o.min_lm_diagonal; a.max_diag = o.max_lm_diagonal;
   a.Hinv = s->Hinv.p; a.ge = s->ge.p; a.diagE = s->diagE.p; a.cost = s->red.p + s->o_cost;
-  a.mode = mode; a.maxposes = s->maxposes; a.maxdz = s->maxdz; a.vwmax = s->vwmax;
+  a.mode = mode; a.want_cost = want_cost ? 1 : 0; a.maxposes = s->maxposes; a.maxdz = s->maxdz; a.vwmax = s->vwmax;
   a.trk_list = nullptr; a.ntrk = v.P;
   if (s->tm) s->tm->begin(9);
   if (s->nchunks > 0 && s->nf > 0 && s->cam_fast) {  // pass A, pose-type columns only: per-image 6 x 6 accumulators, then T'QT
@@ -62,8 +62,9 @@ inline int run_build(mvba_problem* h, const mvba_solve_options& o, double radius
       ta.tile_rounds = s->t2_rounds.p; ta.tile_blob0 = s->t2_blob0.p; ta.tile_bytes0 = s->t2_bytes0.p; ta.blob = s->t2_blob.p; ta.con = s->t_con.p;
       ta.tile_ctr = s->tile_ctr.p; ta.ntiles = s->ntiles; ta.K = s->t2_K; ta.icap = s->t2_icap; ta.ccap = s->t2_ccap; ta.L8max = s->t2_L8max;
       ta.blob_cap = s->t2_blob_cap;
-      if (s->t2_maxs == 8) tile2_kernel<8><<<s->grid_tile2, MVBA_T2_THREADS, s->smem_tile2, h->stream>>>(v, ta, s->R);
-      else tile2_kernel<16><<<s->grid_tile2, MVBA_T2_THREADS, s->smem_tile2, h->stream>>>(v, ta, s->R);
+#define MVBA_T2_LAUNCH(M) case M: tile2_kernel<M><<<s->grid_tile2, MVBA_T2_THREADS, s->smem_tile2, h->stream>>>(v, ta, s->R); break;
+      switch (s->t2_maxs) { MVBA_T2_LAUNCH(4) MVBA_T2_LAUNCH(5) MVBA_T2_LAUNCH(6) MVBA_T2_LAUNCH(7) MVBA_T2_LAUNCH(8) MVBA_T2_LAUNCH(10) MVBA_T2_LAUNCH(12) MVBA_T2_LAUNCH(16) }
+#undef MVBA_T2_LAUNCH
       h->launches++;
     } else if (s->ntiles > 0) {
       TileArgs ta{};
@@ -218,7 +219,7 @@ inline int solver_solve(mvba_problem* h, const mvba_solve_options& o, mvba_summa
     iter++;
     // ---- fused Jacobian + normal equations + Schur elimination at x ----
     tm.begin(PH_BUILD);
-    rc = run_build(h, o, radius, 0, scaled); if (rc) return rc;
+    rc = run_build(h, o, radius, 0, scaled, !have_cost); if (rc) return rc;
     njac++;
     if (!have_cost) { MVBA_CUDA(cudaMemcpyAsync(s->lm.p + LM_COST, s->red.p + s->o_cost, sizeof(double), cudaMemcpyDeviceToDevice, h->stream)); }
     MVBA_CUDA(cudaMemsetAsync(s->lm.p + LM_GMAX, 0, sizeof(double), h->stream));
@@ -296,8 +297,10 @@ inline int solver_solve(mvba_problem* h, const mvba_solve_options& o, mvba_summa
   // gradient tolerance at the final point is checked by the next build in Ceres; the reference's
   // 1e-16 tolerance is never reached in practice, so the last recorded norm is reported.
   MVBA_CUDA(cudaEventRecord(e_all1, h->stream));
-  rc = download_params(h); if (rc) return rc;
+  // an interpolation that left its bracket at ANY evaluated point (the reference aborts there, rig_calibrator.cc:346) is
+  // reported before the write-back: the caller's arrays keep the values they came in with
   rc = check_device_error(h); if (rc) return rc;
+  rc = download_params(h); if (rc) return rc;
   float ms_all = 0;
   MVBA_CUDA(cudaEventElapsedTime(&ms_all, e_all0, e_all1));
   cudaEventDestroy(e_all0); cudaEventDestroy(e_all1);

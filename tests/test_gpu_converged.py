@@ -35,6 +35,12 @@ INTRINSIC = ("focal", "center", "distortion")
 def well_posed(name, seed=23):
     kw = dict(CASES[name])
     kw.update(tri_weight=5.0, tri_robust_threshold=1.0, outlier_frac=0.0)
+    if name == "offsets":
+        # a time offset and the rig translation along the direction of motion are nearly the same direction for this slow,
+        # almost straight trajectory: with both floating the minimum is a long valley that ends on an offset bound, where the
+        # projected steps of either side only creep (radius shrinking every iteration) and no iteration count converges.
+        # The rig is held, the offsets are then determined (to about 1 ms) and the converged state is well defined
+        kw.update(float_rig=False)
     return synth.make_problem(seed=seed, **kw)
 
 
