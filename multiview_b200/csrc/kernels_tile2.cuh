@@ -105,6 +105,61 @@ __device__ __forceinline__ void t2_fetch_landmark(const View& v, const BuildArgs
   } else { dst[3] = 1.0; dst[4] = 1.0; dst[5] = 1.0; }
 }
 
+
+// The image data of one residual block: from the tile's staged copy (STAGED, plain shared-memory loads) or, in tiles whose
+// image range does not fit the staging area, straight from the global table.
+template <bool STAGED>
+__device__ __forceinline__ const CamPack* t2_pack(const CamPack* pack_s, const CamPack* __restrict__ pack_g, int cid, int c0) {
+  return STAGED ? pack_s + (cid - c0) : pack_g + cid;
+}
+
+// One gather group: rows of G = F'E of one (track, parameter block) summed over its contributors.
+template <bool STAGED>
+__device__ __forceinline__ void t2_gather(const int4 raw, const uint16_t* __restrict__ con, const TRec2* rec, const int* rcid,
+                                          const CamPack* pack_s, const CamPack* __restrict__ pack_g, int c0, double (*o)[3]) {
+  const unsigned over0 = (unsigned)raw.x;
+  const int ncon = (int)(((unsigned)raw.y >> 24) & 0x7f);
+  for (int c = 0; c < ncon; c++) {
+    const unsigned cb = c < 4 ? grp_con(raw, c) : __ldg(con + over0 + (c - 4));
+    const int slot = cb >> 2, role = cb & 3;
+    const TRec2& r = rec[slot];
+    const CamPack* cp = t2_pack<STAGED>(pack_s, pack_g, rcid[slot], c0);
+    double M[9];
+#pragma unroll
+    for (int k = 0; k < 9; k++) M[k] = r.M[k];
+    const double* W = role == 2 ? r.y : r.Z;
+    const double W0 = W[0], W1 = W[1], W2 = W[2];
+    double N[9];  // N[:,b] = W x M[:,b]
+#pragma unroll
+    for (int b = 0; b < 3; b++) {
+      N[b] = W1 * M[6 + b] - W2 * M[3 + b];
+      N[3 + b] = W2 * M[b] - W0 * M[6 + b];
+      N[6 + b] = W0 * M[3 + b] - W1 * M[b];
+    }
+    if (role == 3) {  // time offset: d = dalpha (wa x Z + dt)
+      const double* cw = cp->c[21];
+      const double* ce = cp->c[22];
+#pragma unroll
+      for (int b = 0; b < 3; b++)
+        o[0][b] += cw[0] * N[b] + cw[1] * N[3 + b] + cw[2] * N[6 + b] + ce[0] * M[b] + ce[1] * M[3 + b] + ce[2] * M[6 + b];
+    } else {
+      const double(*cr)[3] = cp->c + 7 * role;
+#pragma unroll
+      for (int row = 0; row < 3; row++) {
+        const double f0 = cr[row][0], f1 = cr[row][1], f2 = cr[row][2];
+#pragma unroll
+        for (int b = 0; b < 3; b++) o[row][b] = fma(f0, M[b], fma(f1, M[3 + b], fma(f2, M[6 + b], o[row][b])));
+      }
+#pragma unroll
+      for (int row = 3; row < 7; row++) {
+        const double f0 = cr[row][0], f1 = cr[row][1], f2 = cr[row][2];
+#pragma unroll
+        for (int b = 0; b < 3; b++) o[row][b] = fma(f0, N[b], fma(f1, N[3 + b], fma(f2, N[6 + b], o[row][b])));
+      }
+    }
+  }
+}
+
 #ifdef MVBA_TILE_PROFILE
 #define T2PROF(slot) do { if (tid == 0) { long long now_ = clock64(); prof_[slot] += now_ - tp_; tp_ = now_; } } while (0)
 #else
@@ -150,6 +205,7 @@ __global__ void __launch_bounds__(MVBA_T2_THREADS, 2) tile2_kernel(View v, Tile2
     if (t >= a.ntiles) break;
     const int w0 = a.tile_w0[t], Wt = a.tile_wn[t];
     const int c0 = a.tile_c0[t], nc = a.tile_nc[t];
+    const bool staged = nc > 0;  // the tile's image range fits the staging area (otherwise every access goes to the global table)
     const int nrounds = a.tile_rounds[t];
     const int Lt = 7 * Wt + B;               // local f columns; row Lt carries v = L' E'r
     const int L8 = (Lt + 1 + 7) & ~7;
@@ -161,6 +217,15 @@ __global__ void __launch_bounds__(MVBA_T2_THREADS, 2) tile2_kernel(View v, Tile2
     double acc[MAXS][2];
 #pragma unroll
     for (int i = 0; i < MAXS; i++) { acc[i][0] = 0; acc[i][1] = 0; }
+    int offa[MAXS], offb[MAXS];  // row offsets (doubles) of the two fragments of every block this warp accumulates
+    {
+      int bi = bi0, bj = bj0;
+#pragma unroll
+      for (int sl = 0; sl < MAXS; sl++) {
+        if (sl < ns) { offa[sl] = 8 * bi * KK; offb[sl] = 8 * bj * KK; if (++bj == nb8) { bi++; bj = bi; } }
+        else { offa[sl] = 0; offb[sl] = 0; }
+      }
+    }
     // ---- tile prologue: the window's images and the first round's table by bulk copy; Jacobi scale of the local columns
     int64_t boff = a.tile_blob0[t];
     uint32_t bbytes = a.tile_bytes0[t];
@@ -205,24 +270,37 @@ __global__ void __launch_bounds__(MVBA_T2_THREADS, 2) tile2_kernel(View v, Tile2
         Item it;
         double yv[3] = {0, 0, 0};
         if (kind == 0) {
-          const CamPack* cp = (unsigned)(cid - c0) < (unsigned)nc ? pack_s + (cid - c0) : a.pack + cid;
           it.nr = 2; it.loss_a = v.robust_th;
           const double X0 = Xk[0], X1 = Xk[1], X2 = Xk[2];
-          double Rm[9];
+          double Rm[9], tv[3], dl[3];
+          int sensor;
+          if (staged) {
+            const CamPack* cp = t2_pack<true>(pack_s, a.pack, cid, c0);
 #pragma unroll
-          for (int i = 0; i < 9; i++) Rm[i] = cp->R[i];
+            for (int i = 0; i < 9; i++) Rm[i] = cp->R[i];
+#pragma unroll
+            for (int i = 0; i < 3; i++) { tv[i] = cp->t[i]; dl[i] = cp->dl[i]; }
+            sensor = cp->sensor;
+          } else {
+            const CamPack* cp = t2_pack<false>(pack_s, a.pack, cid, c0);
+#pragma unroll
+            for (int i = 0; i < 9; i++) Rm[i] = __ldg(cp->R + i);
+#pragma unroll
+            for (int i = 0; i < 3; i++) { tv[i] = __ldg(cp->t + i); dl[i] = __ldg(cp->dl + i); }
+            sensor = __ldg(&cp->sensor);
+          }
 #pragma unroll
           for (int i = 0; i < 3; i++) {
             it.Z[i] = Rm[3 * i] * X0 + Rm[3 * i + 1] * X1 + Rm[3 * i + 2] * X2;
-            it.Xc[i] = it.Z[i] + cp->t[i];
-            yv[i] = it.Z[i] + cp->dl[i];
+            it.Xc[i] = it.Z[i] + tv[i];
+            yv[i] = it.Z[i] + dl[i];
           }
-          project_distort<true>(v.sens[cp->sensor], a.b.x, it.Xc, make_float2(sl.px, sl.py), it.r, it.A, it.Jf, &it.Jc, nullptr, nullptr, v.fov_tab + 2 * cp->sensor);
+          project_distort<true>(v.sens[sensor], a.b.x, it.Xc, make_float2(sl.px, sl.py), it.r, it.A, it.Jf, &it.Jc, nullptr, nullptr, v.fov_tab + 2 * sensor);
           it.r[2] = 0;
 #pragma unroll
           for (int i = 0; i < 2; i++)
 #pragma unroll
-            for (int b = 0; b < 3; b++) it.E[3 * i + b] = it.A[3 * i] * cp->R[b] + it.A[3 * i + 1] * cp->R[3 + b] + it.A[3 * i + 2] * cp->R[6 + b];
+            for (int b = 0; b < 3; b++) it.E[3 * i + b] = it.A[3 * i] * Rm[b] + it.A[3 * i + 1] * Rm[3 + b] + it.A[3 * i + 2] * Rm[6 + b];
         } else if (kind <= 2) {
           eval_depth(v, a.b.x, a.b.tab, a.b.dtab, kind == 1 ? MVBA_BLOCK_DEPTH_TRI : MVBA_BLOCK_DEPTH_MESH, sl.a, it);
           const double* trc = a.b.tab[it.cid].trc;
@@ -278,8 +356,12 @@ __global__ void __launch_bounds__(MVBA_T2_THREADS, 2) tile2_kernel(View v, Tile2
         if (tid < kc) {
           const TTrk tk = trk[tid];
           double H[6] = {0, 0, 0, 0, 0, 0}, gE[3] = {0, 0, 0};
+          // lane k starts at its track's block k mod n: neighbouring lanes (tracks, usually n slots apart) then read records
+          // n + 1 slots apart, an odd multiple of the odd record stride -- no bank conflicts
+          const int rot = tk.n > 0 ? tid % tk.n : 0;
           for (int i = 0; i < tk.n; i++) {
-            const TRec2& r = rec[tk.q0 + i];
+            const int ii = i + rot < tk.n ? i + rot : i + rot - tk.n;
+            const TRec2& r = rec[tk.q0 + ii];
 #pragma unroll
             for (int k = 0; k < 6; k++) H[k] += r.H[k];
 #pragma unroll
@@ -314,54 +396,13 @@ __global__ void __launch_bounds__(MVBA_T2_THREADS, 2) tile2_kernel(View v, Tile2
         if (tid < kc_next) t2_fetch_landmark(v, a.b, next_p[tid], Xnext + 6 * tid);
       } else if (tid - 32 < ngrp) {
         const int4 raw = gtab[tid - 32];
-        const unsigned over0 = (unsigned)raw.x;
-        const int nc8 = (int)((unsigned)raw.y >> 24);
-        const bool single = (nc8 & 0x80) != 0;
-        const int ncon = nc8 & 0x7f;
+        const bool single = (((unsigned)raw.y >> 24) & 0x80) != 0;
         g_lcol = raw.y & 0xffff; g_k = (raw.y >> 16) & 0xff; g_rows = single ? 1 : 7;
         double o[7][3];
 #pragma unroll
         for (int r = 0; r < 7; r++) { o[r][0] = 0; o[r][1] = 0; o[r][2] = 0; }
-        for (int c = 0; c < ncon; c++) {
-          const unsigned cb = c < 4 ? grp_con(raw, c) : __ldg(a.con + over0 + (c - 4));
-          const int slot = cb >> 2, role = cb & 3;
-          const TRec2& r = rec[slot];
-          const int cid = rcid[slot];
-          const CamPack* cp = (unsigned)(cid - c0) < (unsigned)nc ? pack_s + (cid - c0) : a.pack + cid;
-          double M[9];
-#pragma unroll
-          for (int k = 0; k < 9; k++) M[k] = r.M[k];
-          const double* W = role == 2 ? r.y : r.Z;
-          const double W0 = W[0], W1 = W[1], W2 = W[2];
-          double N[9];  // N[:,b] = W x M[:,b]
-#pragma unroll
-          for (int b = 0; b < 3; b++) {
-            N[b] = W1 * M[6 + b] - W2 * M[3 + b];
-            N[3 + b] = W2 * M[b] - W0 * M[6 + b];
-            N[6 + b] = W0 * M[3 + b] - W1 * M[b];
-          }
-          if (role == 3) {  // time offset: d = dalpha (wa x Z + dt)
-            const double* cw = cp->c[21];
-            const double* ce = cp->c[22];
-#pragma unroll
-            for (int b = 0; b < 3; b++)
-              o[0][b] += cw[0] * N[b] + cw[1] * N[3 + b] + cw[2] * N[6 + b] + ce[0] * M[b] + ce[1] * M[3 + b] + ce[2] * M[6 + b];
-          } else {
-            const double(*cr)[3] = cp->c + 7 * role;
-#pragma unroll
-            for (int row = 0; row < 3; row++) {
-              const double f0 = cr[row][0], f1 = cr[row][1], f2 = cr[row][2];
-#pragma unroll
-              for (int b = 0; b < 3; b++) o[row][b] = fma(f0, M[b], fma(f1, M[3 + b], fma(f2, M[6 + b], o[row][b])));
-            }
-#pragma unroll
-            for (int row = 3; row < 7; row++) {
-              const double f0 = cr[row][0], f1 = cr[row][1], f2 = cr[row][2];
-#pragma unroll
-              for (int b = 0; b < 3; b++) o[row][b] = fma(f0, N[b], fma(f1, N[3 + b], fma(f2, N[6 + b], o[row][b])));
-            }
-          }
-        }
+        if (staged) t2_gather<true>(raw, a.con, rec, rcid, pack_s, a.pack, c0, o);
+        else t2_gather<false>(raw, a.con, rec, rcid, pack_s, a.pack, c0, o);
 #pragma unroll
         for (int r = 0; r < 7; r++) {
           if (r < g_rows) {
@@ -390,7 +431,6 @@ __global__ void __launch_bounds__(MVBA_T2_THREADS, 2) tile2_kernel(View v, Tile2
           }
         }
       }
-      if (wib == 0) cp_async_wait_all();
       __syncthreads();
       T2PROF(5);
       // the round's table is consumed: fetch the next one while the tensor cores run
@@ -404,15 +444,6 @@ __global__ void __launch_bounds__(MVBA_T2_THREADS, 2) tile2_kernel(View v, Tile2
       {
         const int kend = (3 * kc + 3) & ~3;
         const double* base = Gs + (size_t)gid * KK + tig;
-        int offa[MAXS], offb[MAXS];
-        {
-          int bi = bi0, bj = bj0;
-#pragma unroll
-          for (int sl = 0; sl < MAXS; sl++) {
-            if (sl < ns) { offa[sl] = 8 * bi * KK; offb[sl] = 8 * bj * KK; if (++bj == nb8) { bi++; bj = bi; } }
-            else { offa[sl] = 0; offb[sl] = 0; }
-          }
-        }
 #pragma unroll 2
         for (int k0 = 0; k0 < kend; k0 += 4) {
           const double* kb = base + k0;
@@ -421,6 +452,7 @@ __global__ void __launch_bounds__(MVBA_T2_THREADS, 2) tile2_kernel(View v, Tile2
         }
       }
       T2PROF(6);
+      if (wib == 0) cp_async_wait_all();  // the next round's landmarks (fetched during P2) are in place
       __syncthreads();
       T2PROF(7);
     }

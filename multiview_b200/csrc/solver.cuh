@@ -423,7 +423,7 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
         while (icap + 2 <= MVBA_T2_THREADS && icap < 2 * mean_items * K &&
                tile2_smem(K, icap + 2, s->t2_ccap, s->t2_L8max, (int)t2_blob_bytes(K, K, icap + 2, MVBA_T2_GCAP)) <= budget) icap += 2;
         s->t2_K = K; s->t2_icap = icap; s->t2_blob_cap = (int)t2_blob_bytes(K, K, icap, MVBA_T2_GCAP);
-        for (int t = 0; t < s->ntiles; t++) tnc[t] = std::min(tnc[t], s->t2_ccap);
+        for (int t = 0; t < s->ntiles; t++) if (tnc[t] > s->t2_ccap) tnc[t] = 0;  // range too wide: that tile reads the global table
       }
     }
     s->tile2 = use_t2;
@@ -551,6 +551,7 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
         for (int r = tile_round0[t]; r < tile_round0[t + 1]; r++) { const uint32_t nb = rbytes(r, r + 1 == tile_round0[t + 1]); total += nb; maxbytes = std::max(maxbytes, nb); }
       if ((size_t)maxbytes > (size_t)s->t2_blob_cap) return fail(MVBA_EINVAL, "mvba: round table larger than planned");
       std::vector<uint8_t> blob(std::max<size_t>(total, 16), 0);
+      std::vector<int> rank_of, perm;
       size_t off = 0;
       for (int t = 0; t < s->ntiles; t++) {
         trounds[t] = tile_round0[t + 1] - tile_round0[t];
@@ -581,7 +582,15 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
             }
           }
           q += 16 * (size_t)nit;
-          std::memcpy(q, grp.data() + round_grp0[r], (size_t)ng * sizeof(TGrp));
+          {  // groups ordered by their rank inside their track, then by track: neighbouring gather threads then write different
+             // COLUMNS of Gs (tracks), which spreads over the banks; neighbouring groups of one track would write rows 7 apart
+             // of the same column, 8-way conflicts for a row stride = 4 (mod 16)
+            rank_of.assign(ng, 0); perm.resize(ng);
+            int cnt[32] = {0};
+            for (int g = 0; g < ng; g++) { rank_of[g] = cnt[grp[round_grp0[r] + g].k & 31]++; perm[g] = g; }
+            std::stable_sort(perm.begin(), perm.end(), [&](int x, int y) { return rank_of[x] < rank_of[y]; });
+            for (int g = 0; g < ng; g++) std::memcpy(q + 16 * (size_t)g, &grp[round_grp0[r] + perm[g]], sizeof(TGrp));
+          }
           off += nb;
         }
       }
