@@ -31,15 +31,18 @@ __global__ void jscale_kernel(int64_t n, const double* __restrict__ n2, double* 
   if (i < n) sc[i] = 1.0 / (1.0 + sqrt(n2[i]));
 }
 
-// max |g_i / scale_i| over the f part and the landmark part -> LM_GMAX (bit pattern max).
+// max |g_i / scale_i| over the f part and the landmark part -> *out (bit pattern max, out zeroed before).  `extra`: values
+// that enter the maximum as they are (multi-GPU: the landmark-part maxima of all ranks, which travel in the summed buffer).
 __global__ void gradmax_kernel(int nf, int64_t ne, const double* __restrict__ g, const double* __restrict__ ge,
-                               const double* __restrict__ sf, const double* __restrict__ se, double* __restrict__ lm) {
+                               const double* __restrict__ sf, const double* __restrict__ se, const double* __restrict__ extra, int nextra,
+                               double* __restrict__ out) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   double v = 0;
   if (i < nf) v = fabs(g[i] / (sf ? sf[i] : 1.0));
   else if (i < nf + ne) { int64_t k = i - nf; v = fabs(ge[k] / (se ? se[k] : 1.0)); }
+  else if (i < nf + ne + nextra) v = extra[i - nf - ne];
   for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
-  if ((threadIdx.x & 31) == 0 && v > 0) atomicMax(reinterpret_cast<unsigned long long*>(lm + LM_GMAX), (unsigned long long)__double_as_longlong(v));
+  if ((threadIdx.x & 31) == 0 && v > 0) atomicMax(reinterpret_cast<unsigned long long*>(out), (unsigned long long)__double_as_longlong(v));
 }
 
 // x_new = x - scale * y  over every parameter scalar; accumulates |step|^2 and |x|^2 (free only).

@@ -261,7 +261,7 @@ int mvba_solve_options_init(mvba_solve_options* o) {
 int mvba_solve(mvba_problem* h, const mvba_solve_options* o, mvba_summary* s, mvba_iteration* its, int32_t max_its) {
   int rc = ready(h); if (rc) return rc;
   if (!o || !s) return fail(MVBA_EINVAL, "mvba_solve: null argument");
-  if (o->linear_solver != 0) return fail(MVBA_EINVAL, "mvba_solve: linear_solver must be 0 (PCG on the reduced camera system)");
+  if (o->linear_solver != 0 && o->linear_solver != 1) return fail(MVBA_EINVAL, "mvba_solve: linear_solver must be 0 (PCG on the reduced camera system) or 1 (dense Cholesky)");
   if (o->preconditioner < 0 || o->preconditioner > 2) return fail(MVBA_EINVAL, "mvba_solve: preconditioner must be 0, 1 or 2");
   return solver_solve(h, *o, s, its, max_its);
 }

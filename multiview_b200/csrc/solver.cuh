@@ -14,6 +14,7 @@
 #include "kernels_camq.cuh"
 #include "kernels_tile.cuh"
 #include "kernels_tile2.cuh"
+#include "kernels_chol.cuh"
 
 namespace mvba {
 
@@ -102,7 +103,7 @@ struct Solver {
   int maxposes = 1, maxitems = 1, maxdz = 1, vwmax = MVBA_VPOSE + 4;
   DBuf<int32_t> pairtab, row_ptr, col, slot, xcol, border_blk;
   DBuf<double> red;  // [Spp | Spb | Sbb | Fpp | Fbb | g | diagF | rhs | cost]  (one allreduce)
-  size_t o_Spp = 0, o_Spb = 0, o_Sbb = 0, o_Fpp = 0, o_Fbb = 0, o_g = 0, o_diagF = 0, o_rhs = 0, o_cost = 0, red_n = 0;
+  size_t o_Spp = 0, o_Spb = 0, o_Sbb = 0, o_Fpp = 0, o_Fbb = 0, o_g = 0, o_diagF = 0, o_rhs = 0, o_cost = 0, o_gmaxe = 0, red_n = 0;
   DBuf<double> Dsq, Mpp, Mbb, work, jscale_f, jscale_e, Hinv, ge, diagE, lo, hi;
   DBuf<double> y, r, z, p, q, ye, lm, pcg_scal;
   DBuf<int> pcg_flags;
@@ -134,6 +135,8 @@ struct Solver {
   DBuf<int64_t> t2_blob0; DBuf<uint32_t> t2_bytes0; DBuf<uint8_t> t2_blob;
   int t2_K = 1, t2_icap = 32, t2_ccap = 0, t2_L8max = 8, t2_blob_cap = 64, t2_maxs = 8, grid_tile2 = 1;
   size_t smem_tile2 = 0;
+  // direct solver (linear_solver = 1): dense lower triangle + right-hand-side row, inverses of the diagonal blocks
+  DBuf<double> cholA, cholLinv;
   Reduced R{};
   Bsr A{};
 };
@@ -237,6 +240,7 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
   s->o_Spp = take((size_t)ns * 49); s->o_Spb = take((size_t)s->npc * s->B); s->o_Sbb = take((size_t)s->B * s->B);
   s->o_Fpp = take(with_F ? (size_t)nb * 49 : 0); s->o_Fbb = take(with_F ? (size_t)s->B * s->B : 0);
   s->o_g = take(s->nf); s->o_diagF = take(s->nf); s->o_rhs = take(s->nf); s->o_cost = take(2);
+  s->o_gmaxe = take(std::max(h->nranks, 1));  // one slot per rank: the landmark-part gradient maximum rides in the summed buffer
   s->red_n = o;
   MVBA_CUDA(s->red.alloc(o));
   const int nf = std::max(s->nf, 1);

@@ -111,6 +111,12 @@ inline int run_build(mvba_problem* h, const mvba_solve_options& o, double radius
   }
 #endif
   s->build_launches++;
+  if (mode == 0 && h->nranks > 1 && v.P > 0) {  // this rank's landmark-part gradient maximum, into its own slot of the summed buffer
+    const int64_t ne = 3 * (int64_t)v.P;
+    gradmax_kernel<<<(unsigned)((ne + 255) / 256), 256, 0, h->stream>>>(0, ne, nullptr, s->ge.p, nullptr, a.jscale_e, nullptr, 0,
+                                                                         s->red.p + s->o_gmaxe + h->rank);
+    h->launches++;
+  }
   MVBA_CUDA(cudaGetLastError());
   return allreduce(h, s->red.p, s->red_n, 8, 0);
 }
@@ -173,6 +179,42 @@ inline int run_pcg(mvba_problem* h, const mvba_solve_options& o, int* iters_out)
   return MVBA_OK;
 }
 
+// Direct solve of the reduced camera system: dense blocked Cholesky on the FP64 tensor cores (kernels_chol.cuh).
+inline int run_dense(mvba_problem* h, int* iters_out) {
+  Solver* s = h->solver;
+  const int nf = s->nf;
+  *iters_out = 0;
+  if (nf == 0) return MVBA_OK;
+  if (nf > MVBA_CHOL_MAX_N) return fail(MVBA_EINVAL, "mvba_solve: linear_solver = 1 (dense Cholesky) takes reduced systems of at most 8192 columns");
+  const int NB = MVBA_CHOL_NB, N = (nf + NB - 1) / NB * NB;
+  MVBA_CUDA(s->cholA.alloc((size_t)(N + NB) * N));
+  MVBA_CUDA(s->cholLinv.alloc((size_t)(N / NB) * NB * NB));
+  static bool attr = false;
+  if (!attr) {
+    MVBA_CUDA(cudaFuncSetAttribute(chol_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, MVBA_CHOL_SMEM_DIAG));
+    MVBA_CUDA(cudaFuncSetAttribute(chol_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, MVBA_CHOL_SMEM_GEMM));
+    MVBA_CUDA(cudaFuncSetAttribute(chol_syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, MVBA_CHOL_SMEM_GEMM));
+    MVBA_CUDA(cudaFuncSetAttribute(chol_backsolve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (MVBA_CHOL_MAX_N + 17 * NB) * 8));
+    attr = true;
+  }
+  MVBA_CUDA(s->cholA.zero(h->stream));
+  chol_expand_kernel<<<std::max(1, std::min(4 * h->sm_count, (int)(((int64_t)s->nnzb * 49 + (int64_t)s->npc * s->B + 255) / 256 + 1))), 256, 0, h->stream>>>(
+      s->R, s->A, s->R.rhs, s->cholA.p, N);
+  h->launches++;
+  for (int k = 0; k < N; k += NB) {
+    chol_diag_kernel<<<1, 256, MVBA_CHOL_SMEM_DIAG, h->stream>>>(s->cholA.p, N, k, s->cholLinv.p + (size_t)(k / NB) * NB * NB);
+    const int m = (N - k) / NB;  // tile rows below the panel, the right-hand-side tile included
+    chol_panel_kernel<<<m, 256, MVBA_CHOL_SMEM_GEMM, h->stream>>>(s->cholA.p, N, k, s->cholLinv.p + (size_t)(k / NB) * NB * NB);
+    h->launches += 2;
+    if (m > 1) { chol_syrk_kernel<<<m * (m + 1) / 2, 256, MVBA_CHOL_SMEM_GEMM, h->stream>>>(s->cholA.p, N, k, m); h->launches++; }
+  }
+  chol_backsolve_kernel<<<1, 1024, (size_t)(N + 17 * NB) * 8, h->stream>>>(s->cholA.p, N, nf, s->cholLinv.p, s->y.p);
+  h->launches++;
+  MVBA_CUDA(cudaGetLastError());
+  *iters_out = 1;
+  return MVBA_OK;
+}
+
 inline int run_cost(mvba_problem* h, const double* x, double* out_slot) {
   const View& v = h->view;
   run_prep(h, x);
@@ -223,10 +265,13 @@ inline int solver_solve(mvba_problem* h, const mvba_solve_options& o, mvba_summa
     njac++;
     if (!have_cost) { MVBA_CUDA(cudaMemcpyAsync(s->lm.p + LM_COST, s->red.p + s->o_cost, sizeof(double), cudaMemcpyDeviceToDevice, h->stream)); }
     MVBA_CUDA(cudaMemsetAsync(s->lm.p + LM_GMAX, 0, sizeof(double), h->stream));
-    gradmax_kernel<<<(unsigned)((s->nf + ne + tb - 1) / tb), tb, 0, h->stream>>>(s->nf, ne, s->R.g, s->ge.p, scaled ? s->jscale_f.p : nullptr,
-                                                                                  scaled ? s->jscale_e.p : nullptr, s->lm.p);
+    if (h->nranks > 1)  // the landmark parts of all ranks came with the allreduce of the build (run_build)
+      gradmax_kernel<<<(unsigned)((s->nf + h->nranks + tb - 1) / tb), tb, 0, h->stream>>>(s->nf, 0, s->R.g, nullptr, scaled ? s->jscale_f.p : nullptr, nullptr,
+                                                                                         s->red.p + s->o_gmaxe, h->nranks, s->lm.p + LM_GMAX);
+    else
+      gradmax_kernel<<<(unsigned)((s->nf + ne + tb - 1) / tb), tb, 0, h->stream>>>(s->nf, ne, s->R.g, s->ge.p, scaled ? s->jscale_f.p : nullptr,
+                                                                                    scaled ? s->jscale_e.p : nullptr, nullptr, 0, s->lm.p + LM_GMAX);
     h->launches++;
-    rc = allreduce(h, s->lm.p + LM_GMAX, 1, 5, 2); if (rc) return rc;  // uint64 max of the bit patterns
     if (s->nf) {
       damp_kernel<<<(s->nf + tb - 1) / tb, tb, 0, h->stream>>>(s->R, radius, o.min_lm_diagonal, o.max_lm_diagonal, s->Dsq.p);
       if (s->nb) precond_pose_kernel<<<(s->nb + 63) / 64, 64, 0, h->stream>>>(s->R, s->with_F ? 1 : 0, s->Mpp.p);
@@ -249,7 +294,7 @@ inline int solver_solve(mvba_problem* h, const mvba_solve_options& o, mvba_summa
     // ---- reduced camera system ----
     tm.begin(PH_LINEAR);
     int cgit = 0;
-    rc = run_pcg(h, o, &cgit); if (rc) return rc;
+    rc = o.linear_solver == 1 ? run_dense(h, &cgit) : run_pcg(h, o, &cgit); if (rc) return rc;
     tm.end();
     // ---- back-substitution, candidate point and its cost ----
     tm.begin(PH_UPDATE);
