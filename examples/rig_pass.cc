@@ -20,6 +20,7 @@
 #include "../multiview_b200/host/bracket.h"
 #include "../multiview_b200/host/pass_utils.h"
 #include "../multiview_b200/host/pose_math.h"
+#include "../multiview_b200/host/residual_stats.h"
 #include "../multiview_b200/host/rig_io.h"
 
 using namespace mvba_host;
@@ -161,7 +162,24 @@ int main(int argc, char** argv) {
     mvba_solve_options so; mvba_solve_options_init(&so);
     so.max_num_iterations = std::atoi(opt["num_iterations"].c_str()); so.verbose = 1;
     mvba_summary sum;
+    // residual report before and after the solve (evalResiduals, rig_calibrator.cc:1907 and 1970)
+    auto report = [&](const char* tag) {
+      int64_t nres = 0, nblk = 0;
+      CK(mvba_num_residuals(h, &nres, &nblk));
+      std::vector<int32_t> kind((size_t)nblk); std::vector<int64_t> row0((size_t)nblk), src((size_t)nblk);
+      CK(mvba_residual_layout(h, kind.data(), row0.data(), src.data()));
+      std::vector<double> res((size_t)nres);
+      double cost = 0;
+      CK(mvba_evaluate(h, 0, &cost, res.data()));
+      std::vector<std::string> names, cam_names; std::vector<double> scales;
+      for (int t = 0; t < T; t++) cam_names.push_back(rig.sensors[t].name);
+      const double w4[4] = {0, 0, 0, 0};
+      residual_names_and_scales(nblk, kind.data(), row0.data(), src.data(), o.cid.data(), cam_sensor.data(), cam_names, w4, nres, names, scales);
+      std::fputs(format_residual_stats(calc_residuals_stats(res, names, scales), tag).c_str(), stdout);
+    };
+    report("before opt");
     CK(mvba_solve(h, &so, &sum, nullptr, 0));
+    report("after opt");
     std::printf("pass %d: %zu inlier features, cost %.6e -> %.6e in %d iterations\n", pass, o.pid.size(), sum.initial_cost, sum.final_cost, sum.num_iterations);
     CK(mvba_destroy(h));
     int64_t counts[4];

@@ -338,15 +338,74 @@ __device__ __forceinline__ double spmv_row_dot(const Reduced& S, const Bsr& A, c
   return dot;
 }
 
-__global__ void __launch_bounds__(256) pcg_fused_kernel(Reduced S, Bsr A, const double* Mpp, const double* Mbb, const double* b, double* x,
+
+// Row w of S x with the row's blocks RESIDENT in shared memory (fused PCG: every CTA keeps the blocks of its block rows, and
+// their share of S_pb, for the whole solve; transposed mirror blocks are stored transposed, so the arithmetic of a row is
+// the one of spmv_row_dot, term for term).  sm_pp: blocks of entries [e0, ...), 49 doubles each; sm_pb: rows 7 r0 ... of S_pb.
+template <bool DOT>
+__device__ __forceinline__ double spmv_row_sm(const Reduced& S, const Bsr& A, const double* sm_pp, const double* sm_pb, int e0, int r0,
+                                              const double* x, double* y, int w, int lane) {
+  const int B = S.B;
+  double dot = 0;
+  double acc[7] = {0, 0, 0, 0, 0, 0, 0};
+  for (int e = A.row_ptr[w] + lane; e < A.row_ptr[w + 1]; e += 32) {
+    const int c = A.col[e];
+    const double* xb = x + 7 * c;
+    double xv[7];
+#pragma unroll
+    for (int k = 0; k < 7; k++) xv[k] = xb[k];
+    const double* M = sm_pp + (size_t)(e - e0) * 49;
+#pragma unroll
+    for (int r = 0; r < 7; r++)
+#pragma unroll
+      for (int k = 0; k < 7; k++) acc[r] += M[7 * r + k] * xv[k];
+  }
+  double xr[7];
+#pragma unroll
+  for (int r = 0; r < 7; r++) xr[r] = x[7 * w + r];
+  for (int b = lane; b < B; b += 32) {
+    const double xb = x[S.npc + b];
+    double t = 0;
+#pragma unroll
+    for (int r = 0; r < 7; r++) { const double s = sm_pb[(size_t)(7 * (w - r0) + r) * B + b]; acc[r] += s * xb; t += s * xr[r]; }
+    atomicAdd(y + S.npc + b, t);
+    if (DOT) dot += xb * t;
+  }
+#pragma unroll
+  for (int r = 0; r < 7; r++) acc[r] = warp_sum(acc[r]);
+  if (lane == 0) {
+#pragma unroll
+    for (int r = 0; r < 7; r++) { y[7 * w + r] = acc[r]; if (DOT) dot += xr[r] * acc[r]; }
+  }
+  return dot;
+}
+
+__global__ void __launch_bounds__(512) pcg_fused_kernel(Reduced S, Bsr A, const double* Mpp, const double* Mbb, const double* b, double* x,
                                                          double* r, double* z, double* p, double* q, PcgScal sc, double eta, int min_it,
-                                                         int max_it) {
+                                                         int max_it, int rows_per_cta) {
   namespace cg = cooperative_groups;
   cg::grid_group grid = cg::this_grid();
   const int nf = S.nf, npc = S.npc, B = S.B, nb = S.nb;
   const int gtid = blockIdx.x * blockDim.x + threadIdx.x, nthr = gridDim.x * blockDim.x;
   const int lane = threadIdx.x & 31, gwarp = gtid >> 5, nwarp = nthr >> 5;
   const int sub = lane & 7, gbase = lane & ~7;
+  // rows_per_cta > 0: this CTA owns block rows [r0, r1) and keeps their blocks in shared memory for the whole solve
+  extern __shared__ __align__(16) double pcg_sm[];
+  const int wib = threadIdx.x >> 5, nwib = blockDim.x >> 5;
+  const int r0 = rows_per_cta > 0 ? min(nb, (int)blockIdx.x * rows_per_cta) : 0;
+  const int r1 = rows_per_cta > 0 ? min(nb, r0 + rows_per_cta) : 0;
+  const int e0 = rows_per_cta > 0 ? A.row_ptr[r0] : 0, e1 = rows_per_cta > 0 ? A.row_ptr[r1] : 0;
+  const double* sm_pp = pcg_sm;
+  const double* sm_pb = pcg_sm + (size_t)(e1 - e0) * 49;
+  if (rows_per_cta > 0) {
+    for (int i = threadIdx.x; i < (e1 - e0) * 49; i += blockDim.x) {
+      const int e = e0 + i / 49, rc = i % 49, rr = rc / 7, kk = rc % 7;
+      const int sl = A.slot[e];
+      pcg_sm[i] = sl >= 0 ? S.Spp[(size_t)sl * 49 + rc] : S.Spp[(size_t)(-sl - 1) * 49 + 7 * kk + rr];
+    }
+    double* pb = pcg_sm + (size_t)(e1 - e0) * 49;
+    for (int i = threadIdx.x; i < 7 * (r1 - r0) * B; i += blockDim.x) pb[i] = S.Spb[(size_t)7 * r0 * B + i];
+  }
   for (int i = gtid; i < nf; i += nthr) { x[i] = 0; r[i] = b[i]; }
   grid.sync();
   int done = 0, it_done = 0;
@@ -415,7 +474,12 @@ __global__ void __launch_bounds__(256) pcg_fused_kernel(Reduced S, Bsr A, const 
     // ---- S: q = S p and p.q ----
     {
       double v = 0;
-      for (int w = gwarp; w < nb + B; w += nwarp) v += spmv_row_dot(S, A, p, q, w, lane);
+      if (rows_per_cta > 0) {
+        for (int w = r0 + wib; w < r1; w += nwib) v += spmv_row_sm<true>(S, A, sm_pp, sm_pb, e0, r0, p, q, w, lane);
+        if (blockIdx.x == gridDim.x - 1) for (int w = nb + wib; w < nb + B; w += nwib) v += spmv_row_dot(S, A, p, q, w, lane);
+      } else {
+        for (int w = gwarp; w < nb + B; w += nwarp) v += spmv_row_dot(S, A, p, q, w, lane);
+      }
       block_accumulate(v, sc.it + 4 * it + 1);
     }
     grid.sync();
@@ -426,7 +490,12 @@ __global__ void __launch_bounds__(256) pcg_fused_kernel(Reduced S, Bsr A, const 
     if (it % 10 == 0) {  // residual_reset_period: x updated now, r = b - S x, Q recomputed from it
       for (int i = gtid; i < nf; i += nthr) { x[i] += alpha * p[i]; if (i >= npc) q[i] = 0; }
       grid.sync();
-      for (int w = gwarp; w < nb + B; w += nwarp) spmv_row(S, A, x, q, w, lane);
+      if (rows_per_cta > 0) {
+        for (int w = r0 + wib; w < r1; w += nwib) spmv_row_sm<false>(S, A, sm_pp, sm_pb, e0, r0, x, q, w, lane);
+        if (blockIdx.x == gridDim.x - 1) for (int w = nb + wib; w < nb + B; w += nwib) spmv_row(S, A, x, q, w, lane);
+      } else {
+        for (int w = gwarp; w < nb + B; w += nwarp) spmv_row(S, A, x, q, w, lane);
+      }
       grid.sync();
       double v = 0;
       for (int i = gtid; i < nf; i += nthr) { const double ri = b[i] - q[i]; r[i] = ri; v += -x[i] * (b[i] + ri); }

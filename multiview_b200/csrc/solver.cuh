@@ -114,6 +114,9 @@ struct Solver {
   size_t smem_build = 0, smem_backsub = 0;
   int wpb_build = 8, wpb_backsub = 8, grid_build = 1, grid_backsub = 1;
   int pcg_coop_grid = 0;  // > 0: CTAs of the single-launch PCG (cooperative); 0: step kernels
+  int pcg_rows_per_cta = 0;  // > 0: every CTA keeps the blocks of that many block rows in shared memory for the whole solve
+  size_t smem_pcg = 0;
+  int pcg_threads = 256;
   bool with_F = false;
   // pass A (camera-major F'F): block codes grouped by image, split into chunks
   DBuf<int32_t> citems, chunk_cam, chunk_beg;
@@ -624,11 +627,34 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
   {  // single-launch PCG when the device can co-schedule the grid (MVBA_PCG_STEPS=1 forces the step kernels; developer switch)
     int coop = 0, occ_pcg = 0;
     MVBA_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, h->device));
-    MVBA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_pcg, pcg_fused_kernel, 256, 0));
+    if (const char* evt = std::getenv("MVBA_PCG_THREADS")) { const int t = std::atoi(evt); if (t == 128 || t == 256 || t == 512) s->pcg_threads = t; }
+    MVBA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_pcg, pcg_fused_kernel, s->pcg_threads, 0));
     const char* ev = std::getenv("MVBA_PCG_STEPS");
     if (coop && occ_pcg > 0 && s->nf > 0 && !(ev && ev[0] == '1')) {
       const int want = std::max((s->nb + s->B + 7) / 8, (s->nf + 255) / 256);
       s->pcg_coop_grid = std::max(1, std::min(want, std::min(occ_pcg, 2) * h->sm_count));
+      if (const char* evg = std::getenv("MVBA_PCG_GRID")) { const int g = std::atoi(evg); if (g >= 1) s->pcg_coop_grid = std::min(s->pcg_coop_grid, g); }
+      // the reduced system resident in shared memory across the grid (a few MB over up to 296 CTAs): S is then read from L2
+      // once per solve instead of once per CG iteration.  MVBA_PCG_RESIDENT=0 keeps it in global memory (developer switch)
+      const char* evr = std::getenv("MVBA_PCG_RESIDENT");
+      if (nb > 0 && !(evr && evr[0] == '0')) {
+        for (int grid : {s->pcg_coop_grid, h->sm_count}) {
+          grid = std::max(1, std::min(grid, s->pcg_coop_grid));
+          const int rpc = (nb + grid - 1) / grid;
+          size_t need = 0;
+          for (int r0 = 0; r0 < nb; r0 += rpc) {
+            const int r1 = std::min(nb, r0 + rpc);
+            need = std::max(need, ((size_t)(row_ptr[r1] - row_ptr[r0]) * 49 + (size_t)7 * (r1 - r0) * s->B) * 8);
+          }
+          if (need + 1024 > (size_t)dev_smem) continue;
+          if (cudaFuncSetAttribute(pcg_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)need) != cudaSuccess) { cudaGetLastError(); continue; }
+          int occ_r = 0;
+          MVBA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_r, pcg_fused_kernel, s->pcg_threads, need));
+          if (occ_r * h->sm_count < grid) continue;
+          s->pcg_coop_grid = grid; s->pcg_rows_per_cta = rpc; s->smem_pcg = need;
+          break;
+        }
+      }
     }
   }
   return agree_end.pass();

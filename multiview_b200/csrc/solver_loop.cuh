@@ -138,8 +138,9 @@ inline int run_pcg(mvba_problem* h, const mvba_solve_options& o, int* iters_out)
     const double* Mpp = s->Mpp.p; const double* Mbb = s->Mbb.p; const double* bb = s->R.rhs;
     double *xx = s->y.p, *rr = s->r.p, *zz = s->z.p, *pp = s->p.p, *qq = s->q.p;
     double eta = o.eta; int min_it = o.min_linear_solver_iterations, mx = max_it;
-    void* args[] = {&s->R, &s->A, &Mpp, &Mbb, &bb, &xx, &rr, &zz, &pp, &qq, &sc, &eta, &min_it, &mx};
-    MVBA_CUDA(cudaLaunchCooperativeKernel((const void*)pcg_fused_kernel, dim3(s->pcg_coop_grid), dim3(256), args, 0, h->stream));
+    int rpc = s->pcg_rows_per_cta;
+    void* args[] = {&s->R, &s->A, &Mpp, &Mbb, &bb, &xx, &rr, &zz, &pp, &qq, &sc, &eta, &min_it, &mx, &rpc};
+    MVBA_CUDA(cudaLaunchCooperativeKernel((const void*)pcg_fused_kernel, dim3(s->pcg_coop_grid), dim3(s->pcg_threads), args, s->smem_pcg, h->stream));
     h->launches++;
     // the iteration count lands in pinned memory; the caller reads it after the LM iteration's own synchronisation (-1: deferred)
     MVBA_CUDA(cudaMemcpyAsync(s->flags_host, s->pcg_flags.p, 2 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));

@@ -1,4 +1,5 @@
 // camera_shim.cc -- C test shims over camera::CameraParameters (tests/test_camera_params.py).
+#include <cstring>
 #include <string>
 
 #include "camera_params.h"
@@ -6,6 +7,7 @@
 #include "pass_utils.h"
 #include "pose_math.h"
 #include "bracket.h"
+#include "residual_stats.h"
 
 static thread_local std::string g_cam_err;
 
@@ -124,6 +126,32 @@ int mvh_lookup_images_no_brackets(int num_sensors, const int* counts, const doub
       image_index[i] = b.cams[i].image_index;
     }
     return (int)b.cams.size();
+  } catch (const std::exception& e) { g_cam_err = e.what(); return -1; }
+}
+// residual report of one evaluation (residual_stats.h): cam_names is a '\n'-separated list, one name per sensor; text receives the
+// reference's printout (at most text_cap - 1 characters), table 5 numbers per name (q25 q50 q75 q100 count) in the printed order;
+// returns the number of names, -1 on error
+int mvh_residual_stats(long long num_blocks, const int* kind, const long long* row0, const long long* src, const int* cid, const int* cam_sensor,
+                       const char* cam_names, const double* weights4, long long num_residuals, const double* residuals, const char* tag,
+                       char* text, int text_cap, double* table, int table_cap) {
+  try {
+    std::vector<std::string> names_t;
+    { std::string cur; for (const char* p = cam_names; ; p++) { if (*p == '\n' || *p == 0) { names_t.push_back(cur); cur.clear(); if (*p == 0) break; } else cur.push_back(*p); } }
+    std::vector<int32_t> k32(kind, kind + num_blocks), cid32, cs32;
+    std::vector<int64_t> r64(row0, row0 + num_blocks), s64(src, src + num_blocks);
+    int64_t maxobs = -1; for (long long b = 0; b < num_blocks; b++) if (kind[b] == 0) maxobs = std::max<int64_t>(maxobs, src[b]);
+    cid32.assign(cid, cid + maxobs + 1);
+    int maxcam = -1; for (int c : cid32) maxcam = std::max(maxcam, c);
+    cs32.assign(cam_sensor, cam_sensor + maxcam + 1);
+    std::vector<std::string> names; std::vector<double> scales;
+    mvba_host::residual_names_and_scales(num_blocks, k32.data(), r64.data(), s64.data(), cid32.data(), cs32.data(), names_t, weights4, num_residuals, names, scales);
+    std::vector<mvba_host::ResidualStat> st = mvba_host::calc_residuals_stats(std::vector<double>(residuals, residuals + num_residuals), names, scales);
+    const std::string out = mvba_host::format_residual_stats(st, tag);
+    if (text && text_cap > 0) { const size_t n = std::min<size_t>(out.size(), (size_t)text_cap - 1); std::memcpy(text, out.data(), n); text[n] = 0; }
+    for (size_t i = 0; i < st.size() && (int)(5 * i + 4) < table_cap; i++) {
+      table[5 * i] = st[i].q25; table[5 * i + 1] = st[i].q50; table[5 * i + 2] = st[i].q75; table[5 * i + 3] = st[i].q100; table[5 * i + 4] = (double)st[i].count;
+    }
+    return (int)st.size();
   } catch (const std::exception& e) { g_cam_err = e.what(); return -1; }
 }
 }
