@@ -21,6 +21,7 @@
 #include "../multiview_b200/host/pass_utils.h"
 #include "../multiview_b200/host/pose_math.h"
 #include "../multiview_b200/host/residual_stats.h"
+#include "../multiview_b200/host/rpc_pairs.h"
 #include "../multiview_b200/host/rig_io.h"
 
 using namespace mvba_host;
@@ -188,6 +189,24 @@ int main(int argc, char** argv) {
                 (long long)counts[1], (long long)counts[0], (long long)counts[3], (long long)counts[2]);
   }
   CK(mvba_destroy(h_all));
+
+  // ---- RPC sensors: the undistortion half of the model is re-fitted from its distortion half after the passes
+  //      (rig_calibrator.cc:1946-1948 -> CameraParameters::updateRpcUndistortion); the fit runs on the device (mvba_rpc_fit) ----
+  if (opt.count("refit_rpc_undistortion")) {
+    camera::CameraParameters::SetRpcFitter(&mvba_rpc_fit);
+    for (int t = 0; t < T; t++) {
+      SensorConfig& sc = rig.sensors[t];
+      if (sc.distortion.size() <= 5) continue;
+      try {
+        camera::CameraParameters cp(camera::Vector2i(sc.image_size[0], sc.image_size[1]), camera::Vector2d(focal[t], focal[t]),
+                                    camera::Vector2d(center[2 * t], center[2 * t + 1]), sc.distortion);
+        cp.SetUndistortedSize(camera::Vector2i(sc.undistorted_image_size[0], sc.undistorted_image_size[1]));
+        cp.SetDistortedCropSize(camera::Vector2i(sc.distorted_crop_size[0], sc.distorted_crop_size[1]));
+        cp.updateRpcUndistortion(1);
+        sc.distortion = cp.GetDistortion();
+      } catch (const std::exception& e) { die(e.what()); }
+    }
+  }
 
   // ---- copy-back and outputs (rig_calibrator.cc:1924-1967; dense_map_utils.cc:753-850; interest_point.cc:1338-1475) ----
   for (int t = 0; t < T; t++) { rig.sensors[t].ref_to_sensor = array_to_rigid(&ref_to_cam[7 * (size_t)t]); rig.sensors[t].ref_to_sensor_timestamp_offset = offsets[t]; }

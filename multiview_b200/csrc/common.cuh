@@ -45,6 +45,12 @@ struct alignas(16) CamPack {
 };
 static_assert(sizeof(CamPack) == 688 && sizeof(CamPack) % 16 == 0, "CamPack layout");
 
+// One residual block in a host-packed list (the rounds of kernels_tile2.cuh, the camera-major list of kernels_camq.cuh): CAM blocks carry everything the evaluation needs (a = landmark, unused here: the
+// landmark comes from the track slot), other kinds their index inside the kind's array.
+//   b = image | kind << 24 | track slot << 27    (kind 0 CAM, 1 DEPTH_TRI, 2 DEPTH_MESH, 3 MESH_TRI prior, 4 TRI prior)
+struct alignas(16) TSlot { int32_t a; uint32_t b; float px, py; };
+static_assert(sizeof(TSlot) == 16, "TSlot layout");
+
 // Per-sensor depth-to-image table (prep_sensors_kernel): Mc = s L m + td
 struct DepthTab {
   double L[9], td[3], s;

@@ -182,4 +182,37 @@ __global__ void __launch_bounds__(128, 4) backsub_kernel(View v, BacksubArgs a) 
   block_accumulate(mcc, a.lm + a.lm_mcc);
 }
 
+// Squared column norms of the landmark part of the (loss-corrected, unscaled) Jacobian: diag(E'E) per landmark, one thread
+// per track.  Ceres' Jacobi scaling is computed once per solve from these (TrustRegionMinimizer::Init); F's share comes from pass A.
+__global__ void __launch_bounds__(128, 4) colnorm_e_kernel(View v, const double* __restrict__ x, const CamTab* __restrict__ tab,
+                                                           const DepthTab* __restrict__ dtab, double* __restrict__ diagE) {
+  for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < v.P; p += gridDim.x * blockDim.x) {
+    const int64_t r0[5] = {v.trk_obs0[p], v.trk_dtri0[p], v.trk_dmesh0[p], v.trk_pm0[p], v.trk_pt0[p]};
+    const int64_t r1[5] = {v.trk_obs0[p + 1], v.trk_dtri0[p + 1], v.trk_dmesh0[p + 1], v.trk_pm0[p + 1], v.trk_pt0[p + 1]};
+    double H[3] = {0, 0, 0};
+#pragma unroll
+    for (int kind = 0; kind < 5; kind++) {
+      for (int64_t j = r0[kind]; j < r1[kind]; j++) {
+        Item it;
+        if (kind == 0) eval_cam<true>(v, x, tab, j, it, nullptr, nullptr);
+        else if (kind == 1) eval_depth(v, x, tab, dtab, MVBA_BLOCK_DEPTH_TRI, j, it);
+        else if (kind == 2) eval_depth(v, x, tab, dtab, MVBA_BLOCK_DEPTH_MESH, j, it);
+        else eval_prior(v, x, j, it);
+        const int nr = kind == 0 ? 2 : 3;
+        double s = it.r[0] * it.r[0] + it.r[1] * it.r[1];
+        if (nr == 3) s += it.r[2] * it.r[2];
+        const double sr = cauchy_sr(it.loss_a, s);
+#pragma unroll
+        for (int r = 0; r < 3; r++) {
+          if (r < nr) {
+#pragma unroll
+            for (int b = 0; b < 3; b++) { const double e = sr * it.E[3 * r + b]; H[b] += e * e; }
+          }
+        }
+      }
+    }
+    diagE[3 * (size_t)p] = H[0]; diagE[3 * (size_t)p + 1] = H[1]; diagE[3 * (size_t)p + 2] = H[2];
+  }
+}
+
 }  // namespace mvba

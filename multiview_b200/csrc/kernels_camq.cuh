@@ -27,6 +27,8 @@ struct CamQArgs {
   const int32_t* chunk_cam;    // per chunk: camera image
   const int32_t* chunk_beg;    // nchunks + 1: range into citems
   const int32_t* citems;       // block codes, camera-major: [0,N) CAM, then DEPTH_TRI, then DEPTH_MESH
+  const TSlot* crec;           // the same list as packed records: CAM blocks carry landmark and pixel (a = pid, b = kind << 24, px, py),
+                               // the depth kinds their index inside the kind (a)
   int nchunks;
   double* Q;                   // C x MVBA_CAMQ_N, zeroed before the launch
 };
@@ -40,12 +42,35 @@ __global__ void __launch_bounds__(256, 2) camq_kernel(View v, CamQArgs a) {
     double q[27];
 #pragma unroll
     for (int k = 0; k < 27; k++) q[k] = 0;
+    // the chunk's image: rotation, translation and sensor are the same for every block (broadcast loads, then registers)
+    double Rm[9], tv[3];
+    {
+      const CamTab& ct = a.tab[cam];
+#pragma unroll
+      for (int k = 0; k < 9; k++) Rm[k] = __ldg(ct.R + k);
+#pragma unroll
+      for (int k = 0; k < 3; k++) tv[k] = __ldg(ct.t + k);
+    }
+    const int sensor = v.cam_sensor[cam];
     for (int i = i0 + tid; i < i1; i += 256) {
-      const int64_t code = a.citems[i];
+      const int4 raw = __ldg(reinterpret_cast<const int4*>(a.crec) + i);
+      TSlot sl; sl.a = raw.x; sl.b = (uint32_t)raw.y; sl.px = __int_as_float(raw.z); sl.py = __int_as_float(raw.w);  // one coalesced 16-byte record per block: no index chain in front of the landmark gather
+      const int kind = (sl.b >> 24) & 7;
       Item it;
-      if (code < v.N) eval_cam<true, false>(v, a.x, a.tab, code, it, nullptr, nullptr);
-      else if (code < v.N + v.n_dtri) eval_depth(v, a.x, a.tab, a.dtab, MVBA_BLOCK_DEPTH_TRI, code - v.N, it);
-      else eval_depth(v, a.x, a.tab, a.dtab, MVBA_BLOCK_DEPTH_MESH, code - v.N - v.n_dtri, it);
+      if (kind == 0) {
+        const double* X = a.x + v.x_xyz + 3 * (int64_t)sl.a;
+        const double X0 = X[0], X1 = X[1], X2 = X[2];
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+          it.Z[k] = Rm[3 * k] * X0 + Rm[3 * k + 1] * X1 + Rm[3 * k + 2] * X2;
+          it.Xc[k] = it.Z[k] + tv[k];
+        }
+        it.nr = 2; it.loss_a = v.robust_th;
+        project_distort<true>(v.sens[sensor], a.x, it.Xc, make_float2(sl.px, sl.py), it.r, it.A, it.Jf, &it.Jc, nullptr, nullptr, v.fov_tab + 2 * sensor);
+        it.r[2] = 0;
+      } else {
+        eval_depth(v, a.x, a.tab, a.dtab, kind == 1 ? MVBA_BLOCK_DEPTH_TRI : MVBA_BLOCK_DEPTH_MESH, sl.a, it);
+      }
       double s = it.r[0] * it.r[0] + it.r[1] * it.r[1];
       if (it.nr == 3) s += it.r[2] * it.r[2];
       double hr, sr;

@@ -19,9 +19,10 @@ enum {
   LM_GMAX = 7,        // gradient max norm (as double)
   LM_RELDEC = 8,
   LM_ACCEPT = 9,      // 1.0 when the step was accepted
-  LM_TERM = 10,       // 0 continue, 1 parameter tol, 2 function tol, 3 gradient tol, 4 min radius
+  LM_TERM = 10,       // 0 continue, 1 parameter tol, 2 function tol, 3 gradient tol, 4 min radius, 5 too many invalid steps
   LM_STEP2 = 11,      // |step|^2, replicated (non-landmark) part
   LM_XNORM2 = 12,     // |x|^2, replicated part
+  LM_INVALID = 13,    // consecutive invalid steps (model cost change not positive)
   LM_NSLOTS = 16
 };
 
@@ -42,7 +43,15 @@ __global__ void gradmax_kernel(int nf, int64_t ne, const double* __restrict__ g,
   else if (i < nf + ne) { int64_t k = i - nf; v = fabs(ge[k] / (se ? se[k] : 1.0)); }
   else if (i < nf + ne + nextra) v = extra[i - nf - ne];
   for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
-  if ((threadIdx.x & 31) == 0 && v > 0) atomicMax(reinterpret_cast<unsigned long long*>(out), (unsigned long long)__double_as_longlong(v));
+  __shared__ double wmax[32];  // one atomic per CTA: a per-warp atomic on ONE address serialises ~100 k updates at 3 M landmarks
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (lane == 0) wmax[w] = v;
+  __syncthreads();
+  if (w == 0) {
+    v = lane < (int)(blockDim.x >> 5) ? wmax[lane] : 0.0;
+    for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+    if (lane == 0 && v > 0) atomicMax(reinterpret_cast<unsigned long long*>(out), (unsigned long long)__double_as_longlong(v));
+  }
 }
 
 // x_new = x - scale * y  over every parameter scalar; accumulates |step|^2 and |x|^2 (free only).
@@ -73,7 +82,7 @@ __global__ void __launch_bounds__(256) update_kernel(int nx, int nf, const int32
   block_accumulate(is_e ? x2 : 0.0, lm + LM_XNORM2E);
 }
 
-struct LmOpts { double min_rel_dec, param_tol, func_tol, max_radius, min_radius; };
+struct LmOpts { double min_rel_dec, param_tol, func_tol, max_radius, min_radius, grad_tol; };
 
 // Single thread: accept/reject and radius update (LevenbergMarquardtStrategy::StepAccepted/Rejected).
 __global__ void lm_decide_kernel(double* __restrict__ lm, LmOpts o, mvba_iteration* __restrict__ rec, int cg_iters_dummy) {
@@ -82,9 +91,17 @@ __global__ void lm_decide_kernel(double* __restrict__ lm, LmOpts o, mvba_iterati
   double radius = lm[LM_RADIUS], dec = lm[LM_DECREASE];
   int accept = 0, term = 0;
   double change = 0, rel = 0;
-  if (!(mcc > 0) || !isfinite(mcc)) {
+  double invalid = lm[LM_INVALID];
+  if (lm[LM_GMAX] <= o.grad_tol) {
+    // the gradient at x (this iteration's build) is within tolerance: Ceres stops right after the step that led here
+    // (TrustRegionMinimizer::HandleSuccessfulStep); the step computed meanwhile is dropped, x stays
+    term = 3;
+  } else if (!(mcc > 0) || !isfinite(mcc)) {
     radius /= dec; dec *= 2;
+    invalid += 1.0;
+    if (invalid >= 5.0) term = 5;  // max_num_consecutive_invalid_steps (Ceres default)
   } else {
+    invalid = 0.0;
     if (!isfinite(cand)) cand = 1.7976931348623157e308;
     change = cost - cand;
     rel = change / mcc;
@@ -103,7 +120,7 @@ __global__ void lm_decide_kernel(double* __restrict__ lm, LmOpts o, mvba_iterati
   }
   if (radius < o.min_radius && term == 0) term = 4;
   lm[LM_COST] = cost; lm[LM_RADIUS] = radius; lm[LM_DECREASE] = dec; lm[LM_RELDEC] = rel;
-  lm[LM_ACCEPT] = accept; lm[LM_TERM] = term;
+  lm[LM_ACCEPT] = accept; lm[LM_TERM] = term; lm[LM_INVALID] = invalid;
   rec->cost = cost; rec->cost_change = change; rec->step_norm = step; rec->relative_decrease = rel; rec->radius = radius;
   rec->step_accepted = accept; rec->gradient_max_norm = lm[LM_GMAX]; rec->linear_iterations = term;
 }

@@ -67,10 +67,11 @@ __device__ __forceinline__ bool ray_tri(const float* o, const float* d, float tm
 }
 
 #define MVBA_BAD_XYZ 1e100  // bad_xyz, rig_calibrator.cc:1546
+#define MVBA_BVH_STACK 64   // traversal stack entries; the host refuses deeper trees (a median-split tree over 2^31 triangles has 30 levels)
 
 __global__ void mesh_intersect_kernel(View v, const double* __restrict__ x, const CamTab* __restrict__ tab, const BvhNode* __restrict__ nodes,
                                       const MeshTri* __restrict__ tris, double min_ray_dist, double max_ray_dist,
-                                      const uint8_t* __restrict__ inlier, uint8_t* __restrict__ has_mesh, double* __restrict__ mesh_xyz) {
+                                      const uint8_t* __restrict__ inlier, uint8_t* __restrict__ has_mesh, double* __restrict__ mesh_xyz, int* __restrict__ err) {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < v.N; i += (int64_t)gridDim.x * blockDim.x) {
     double out[3] = {MVBA_BAD_XYZ, MVBA_BAD_XYZ, MVBA_BAD_XYZ};
     uint8_t hit_any = 0;
@@ -100,7 +101,7 @@ __global__ void mesh_intersect_kernel(View v, const double* __restrict__ x, cons
       const float tmin = (float)min_ray_dist;
       float tmax = (float)max_ray_dist;
       float best = __int_as_float(0x7f800000);
-      int stack[64], sp = 0;
+      int stack[MVBA_BVH_STACK], sp = 0;
       stack[sp++] = 0;
       while (sp > 0) {
         const BvhNode& n = nodes[stack[--sp]];
@@ -113,7 +114,7 @@ __global__ void mesh_intersect_kernel(View v, const double* __restrict__ x, cons
             if (hr) stack[sp++] = n.right;
             if (hl) stack[sp++] = n.left;
           }
-          if (sp > 62) sp = 62;  // deeper than any tree the builder makes
+          if (sp > MVBA_BVH_STACK - 2) { atomicExch(err, MVBA_EINVAL); break; }  // cannot happen for a tree the host accepted; never truncate silently
         } else {
           for (int k = n.first; k < n.first + n.count; k++) {
             float tt;

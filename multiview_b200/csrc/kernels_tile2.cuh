@@ -26,12 +26,8 @@ namespace mvba {
 #define MVBA_T2_THREADS 256
 #define MVBA_T2_GCAP (MVBA_T2_THREADS - 32)  // gather groups of one round (one thread each, warp 0 inverts)
 
-// One residual block of a round: CAM blocks carry everything the evaluation needs (a = landmark, unused here: the
-// landmark comes from the track slot), other kinds their index inside the kind's array.
-//   b = image | kind << 24 | track slot << 27    (kind 0 CAM, 1 DEPTH_TRI, 2 DEPTH_MESH, 3 MESH_TRI prior, 4 TRI prior)
-struct alignas(16) TSlot { int32_t a; uint32_t b; float px, py; };
 struct alignas(16) TRoundHdr { int32_t kc, nit, ngrp, kc_next; uint32_t next_bytes; int32_t pad[3]; };
-static_assert(sizeof(TSlot) == 16 && sizeof(TRoundHdr) == 32, "round blob layout");
+static_assert(sizeof(TRoundHdr) == 32, "round blob layout");
 __host__ __device__ inline uint32_t t2_align16(uint32_t n) { return (n + 15u) & ~15u; }
 // blob: TRoundHdr | TTrk[kc] | int32 next_p[kc_next] | TSlot[nit] | TGrp[ngrp], every part 16-byte aligned
 __host__ __device__ inline uint32_t t2_blob_bytes(int kc, int kc_next, int nit, int ngrp) {
@@ -42,6 +38,11 @@ __host__ __device__ inline uint32_t t2_blob_bytes(int kc, int kc_next, int nit, 
 // (a 24-double record puts every slot in one of two bank groups: 16-way conflicts on each access)
 struct TRec2 { double M[9], Z[3], y[3], H[6], g[3], pad; };
 static_assert(sizeof(TRec2) == 200, "TRec2 layout");
+// Where slot q's record lives: one record is skipped after every eight.  Neighbouring gather threads read the records of
+// neighbouring TRACKS, usually eight slots apart: 8 x 25 doubles is 8 (mod 16) -- two bank positions, 16-way conflicts --
+// while 9 x 25 is 1 (mod 16).
+__host__ __device__ inline int t2_rslot(int q) { return q + (q >> 3); }
+__host__ __device__ inline int t2_rcap(int icap) { return icap + (icap >> 3) + 1; }
 
 struct Tile2Args {
   BuildArgs b;
@@ -60,14 +61,14 @@ struct Tile2Args {
   int K, icap, ccap, L8max, blob_cap;
 };
 
-// Shared memory: Gs[L8max][KK] | pack[ccap] | blob | Xs[2][K][6] | Ls[K][6] | cs[L8max] | rec[icap] | rcid[icap] | mbarriers
+// Shared memory: Gs[L8max][KK] | pack[ccap] | blob | Xs[2][K][6] | Ls[K][6] | cs[L8max] | rec[icap + icap / 8 + 1] | rcid[same] | mbarriers
 // (the bulk-copy destinations first: they need 16-byte alignment)
 __host__ __device__ inline size_t tile2_smem(int K, int icap, int ccap, int L8max, int blob_cap) {
   const size_t KK = tile_kk(K);
   size_t n = (size_t)L8max * KK * 8 + (size_t)ccap * sizeof(CamPack) + (size_t)blob_cap;
   n += ((size_t)2 * K * 6 + (size_t)K * 6 + (size_t)L8max) * 8;
-  n += (size_t)icap * sizeof(TRec2);
-  n += (((size_t)icap * 4 + 7) & ~(size_t)7) + 16;
+  n += (size_t)t2_rcap(icap) * sizeof(TRec2);
+  n += (((size_t)t2_rcap(icap) * 4 + 7) & ~(size_t)7) + 16;
   return n + 16;
 }
 
@@ -122,8 +123,8 @@ __device__ __forceinline__ void t2_gather(const int4 raw, const uint16_t* __rest
   for (int c = 0; c < ncon; c++) {
     const unsigned cb = c < 4 ? grp_con(raw, c) : __ldg(con + over0 + (c - 4));
     const int slot = cb >> 2, role = cb & 3;
-    const TRec2& r = rec[slot];
-    const CamPack* cp = t2_pack<STAGED>(pack_s, pack_g, rcid[slot], c0);
+    const TRec2& r = rec[t2_rslot(slot)];
+    const CamPack* cp = t2_pack<STAGED>(pack_s, pack_g, rcid[t2_rslot(slot)], c0);
     double M[9];
 #pragma unroll
     for (int k = 0; k < 9; k++) M[k] = r.M[k];
@@ -180,8 +181,8 @@ __global__ void __launch_bounds__(MVBA_T2_THREADS, 2) tile2_kernel(View v, Tile2
   double* Ls = Xs + (size_t)2 * K * 6;
   double* cs = Ls + (size_t)K * 6;
   TRec2* rec = reinterpret_cast<TRec2*>(cs + a.L8max);
-  int* rcid = reinterpret_cast<int*>(rec + a.icap);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<unsigned char*>(rcid) + (((size_t)a.icap * 4 + 7) & ~(size_t)7));
+  int* rcid = reinterpret_cast<int*>(rec + t2_rcap(a.icap));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(reinterpret_cast<unsigned char*>(rcid) + (((size_t)t2_rcap(a.icap) * 4 + 7) & ~(size_t)7));
   uint64_t* bar_blob = bars;
   uint64_t* bar_pack = bars + 1;
   __shared__ int s_tile;
@@ -218,12 +219,17 @@ __global__ void __launch_bounds__(MVBA_T2_THREADS, 2) tile2_kernel(View v, Tile2
 #pragma unroll
     for (int i = 0; i < MAXS; i++) { acc[i][0] = 0; acc[i][1] = 0; }
     int offa[MAXS], offb[MAXS];  // row offsets (doubles) of the two fragments of every block this warp accumulates
+    unsigned newrow = 0;         // bit sl: block sl starts a new block row (its A fragment has to be loaded)
     {
-      int bi = bi0, bj = bj0;
+      int bi = bi0, bj = bj0, prev = -1;
 #pragma unroll
       for (int sl = 0; sl < MAXS; sl++) {
-        if (sl < ns) { offa[sl] = 8 * bi * KK; offb[sl] = 8 * bj * KK; if (++bj == nb8) { bi++; bj = bi; } }
-        else { offa[sl] = 0; offb[sl] = 0; }
+        if (sl < ns) {
+          offa[sl] = 8 * bi * KK; offb[sl] = 8 * bj * KK;
+          if (bi != prev) newrow |= 1u << sl;
+          prev = bi;
+          if (++bj == nb8) { bi++; bj = bi; }
+        } else { offa[sl] = sl ? offa[0] : 0; offb[sl] = sl ? offb[0] : 0; }
       }
     }
     // ---- tile prologue: the window's images and the first round's table by bulk copy; Jacobi scale of the local columns
@@ -327,12 +333,12 @@ __global__ void __launch_bounds__(MVBA_T2_THREADS, 2) tile2_kernel(View v, Tile2
           H[0] += e[0] * e[0]; H[1] += e[0] * e[1]; H[2] += e[0] * e[2]; H[3] += e[1] * e[1]; H[4] += e[1] * e[2]; H[5] += e[2] * e[2];
           g[0] += e[0] * rs; g[1] += e[1] * rs; g[2] += e[2] * rs;
         }
-        TRec2& rc = rec[tid];
+        TRec2& rc = rec[t2_rslot(tid)];
 #pragma unroll
         for (int k = 0; k < 6; k++) rc.H[k] = H[k];
 #pragma unroll
         for (int k = 0; k < 3; k++) rc.g[k] = g[k];
-        rcid[tid] = kind >= 3 ? -1 : cid;
+        rcid[t2_rslot(tid)] = kind >= 3 ? -1 : cid;
         if (kind < 3) {
 #pragma unroll
           for (int k = 0; k < 3; k++) { rc.Z[k] = it.Z[k]; rc.y[k] = yv[k]; }
@@ -361,7 +367,7 @@ __global__ void __launch_bounds__(MVBA_T2_THREADS, 2) tile2_kernel(View v, Tile2
           const int rot = tk.n > 0 ? tid % tk.n : 0;
           for (int i = 0; i < tk.n; i++) {
             const int ii = i + rot < tk.n ? i + rot : i + rot - tk.n;
-            const TRec2& r = rec[tk.q0 + ii];
+            const TRec2& r = rec[t2_rslot(tk.q0 + ii)];
 #pragma unroll
             for (int k = 0; k < 6; k++) H[k] += r.H[k];
 #pragma unroll
@@ -447,8 +453,14 @@ __global__ void __launch_bounds__(MVBA_T2_THREADS, 2) tile2_kernel(View v, Tile2
 #pragma unroll 2
         for (int k0 = 0; k0 < kend; k0 += 4) {
           const double* kb = base + k0;
+          double av = kb[offa[0]];
 #pragma unroll
-          for (int sl = 0; sl < MAXS; sl++) dmma884(acc[sl][0], acc[sl][1], kb[offa[sl]], kb[offb[sl]]);
+          for (int sl = 0; sl < MAXS; sl++) {
+            if (sl < ns) {  // warp-uniform: the last warp usually owns fewer blocks, and an idle DMMA would still take its pipe slot
+              if (sl > 0 && ((newrow >> sl) & 1)) av = kb[offa[sl]];  // the A fragment stays while the warp's blocks stay in one block row
+              dmma884(acc[sl][0], acc[sl][1], av, kb[offb[sl]]);
+            }
+          }
         }
       }
       T2PROF(6);

@@ -357,19 +357,22 @@ int mvba_flag_exclusion(mvba_problem* h, const double* image_size, const double*
 }
 
 // Median-split hierarchy over the triangles (host): nodes in depth-first order, triangles reordered leaf by leaf.
-static void build_bvh(const std::vector<mvba::MeshTri>& in, std::vector<mvba::BvhNode>& nodes, std::vector<mvba::MeshTri>& out) {
+// Returns the depth of the tree (root = 1): the traversal kernel keeps one stack entry per level.
+static int build_bvh(const std::vector<mvba::MeshTri>& in, std::vector<mvba::BvhNode>& nodes, std::vector<mvba::MeshTri>& out) {
   const int n = (int)in.size();
   std::vector<int> idx(n);
   for (int i = 0; i < n; i++) idx[i] = i;
   std::vector<std::array<float, 3>> cen(n);
   for (int i = 0; i < n; i++) for (int a = 0; a < 3; a++) cen[i][a] = (in[i].a[a] + in[i].b[a] + in[i].c[a]) / 3.0f;
-  struct Job { int node, first, last; };
+  struct Job { int node, first, last, depth; };
   std::vector<Job> todo;
+  int max_depth = 0;
   nodes.clear(); out.clear();
   nodes.push_back(mvba::BvhNode{});
-  todo.push_back({0, 0, n});
+  todo.push_back({0, 0, n, 1});
   while (!todo.empty()) {
     const Job j = todo.back(); todo.pop_back();
+    max_depth = std::max(max_depth, j.depth);
     mvba::BvhNode nd{};
     float clo[3], chi[3];
     for (int a = 0; a < 3; a++) { nd.lo[a] = clo[a] = 3.4e38f; nd.hi[a] = chi[a] = -3.4e38f; }
@@ -392,11 +395,12 @@ static void build_bvh(const std::vector<mvba::MeshTri>& in, std::vector<mvba::Bv
       std::nth_element(idx.begin() + j.first, idx.begin() + mid, idx.begin() + j.last, [&](int p, int q) { return cen[p][axis] < cen[q][axis]; });
       nd.left = (int)nodes.size(); nodes.push_back(mvba::BvhNode{});
       nd.right = (int)nodes.size(); nodes.push_back(mvba::BvhNode{});
-      todo.push_back({nd.left, j.first, mid});
-      todo.push_back({nd.right, mid, j.last});
+      todo.push_back({nd.left, j.first, mid, j.depth + 1});
+      todo.push_back({nd.right, mid, j.last, j.depth + 1});
     }
     nodes[j.node] = nd;
   }
+  return max_depth;
 }
 
 int mvba_mesh_intersect(mvba_problem* h, int64_t num_vertices, const float* vertices, int64_t num_faces, const uint32_t* faces,
@@ -413,14 +417,15 @@ int mvba_mesh_intersect(mvba_problem* h, int64_t num_vertices, const float* vert
     }
   }
   std::vector<mvba::BvhNode> nodes;
-  build_bvh(tris, nodes, sorted);
+  const int depth = build_bvh(tris, nodes, sorted);
+  if (depth + 2 > MVBA_BVH_STACK) return fail(MVBA_EINVAL, "mvba_mesh_intersect: BVH deeper than the traversal stack");
   MVBA_CUDA(d_nodes.upload(nodes)); MVBA_CUDA(d_tris.upload(sorted));
   const View& v = h->view;
   MVBA_CUDA(d_has.alloc((size_t)std::max<int64_t>(v.N, 1))); MVBA_CUDA(d_xyz.alloc((size_t)3 * std::max<int64_t>(v.N, 1)));
   MVBA_CUDA(d_mean.alloc((size_t)3 * std::max(v.P, 1)));
   if (v.N > 0) {
     const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((v.N + 127) / 128, (int64_t)h->sm_count * 16));
-    mesh_intersect_kernel<<<grid, 128, 0, h->stream>>>(v, h->d_x.p, h->d_tab.p, d_nodes.p, d_tris.p, min_ray_dist, max_ray_dist, d_in.p, d_has.p, d_xyz.p);
+    mesh_intersect_kernel<<<grid, 128, 0, h->stream>>>(v, h->d_x.p, h->d_tab.p, d_nodes.p, d_tris.p, min_ray_dist, max_ray_dist, d_in.p, d_has.p, d_xyz.p, h->d_err.p);
     const int grid2 = std::max(1, std::min((v.P + 127) / 128, h->sm_count * 16));
     mesh_track_mean_kernel<<<grid2, 128, 0, h->stream>>>(v, d_has.p, d_xyz.p, d_mean.p);
     h->launches += 2;
@@ -428,6 +433,8 @@ int mvba_mesh_intersect(mvba_problem* h, int64_t num_vertices, const float* vert
     MVBA_CUDA(cudaMemcpyAsync(has_mesh, d_has.p, (size_t)v.N, cudaMemcpyDeviceToHost, h->stream));
     MVBA_CUDA(cudaMemcpyAsync(mesh_xyz, d_xyz.p, sizeof(double) * 3 * v.N, cudaMemcpyDeviceToHost, h->stream));
     if (pid_mesh_xyz) MVBA_CUDA(cudaMemcpyAsync(pid_mesh_xyz, d_mean.p, sizeof(double) * 3 * v.P, cudaMemcpyDeviceToHost, h->stream));
+  } else if (pid_mesh_xyz) {
+    for (size_t i = 0; i < (size_t)3 * v.P; i++) pid_mesh_xyz[i] = MVBA_BAD_XYZ;  // no feature, no hit: every track gets bad_xyz
   }
   return check_device_error(h);
 }

@@ -125,6 +125,7 @@ struct Solver {
   // pass A without free intrinsics / depth columns: per-image 6 x 6 accumulators (kernels_camq.cuh)
   bool cam_fast = false;
   DBuf<double> camQ;
+  DBuf<TSlot> crec;  // camera-major packed records (pass A without staged rows)
   int grid_camq = 1;
   // pass B fast path: tracks sorted by first pose block and cut into window tiles; the rest fall back
   // (static round tables: staged blocks, per-track slots, gather groups and their contributors, kernels_tile.cuh)
@@ -263,6 +264,7 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
   R.g = rb + s->o_g; R.diagF = rb + s->o_diagF; R.rhs = rb + s->o_rhs;
   R.pairtab = s->pairtab.p; R.nb = nb; R.npc = s->npc; R.B = s->B; R.nf = s->nf;
   s->A.row_ptr = s->row_ptr.p; s->A.col = s->col.p; s->A.slot = s->slot.p; s->A.nb = nb;
+  std::vector<int32_t> cam_items_host;
   {  // ---- pass A: residual blocks with f columns grouped by camera image (counting sort), chunked ----
     const int64_t nit = v.N + v.n_dtri + v.n_dmesh;
     if (nit >= ((int64_t)1 << 31)) return fail(MVBA_EINVAL, "mvba: more than 2^31 residual blocks on one device");
@@ -276,6 +278,7 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
     for (int c = 0; c < v.C; c++) cnt[c + 1] += cnt[c];
     std::vector<int32_t> items((size_t)nit), fill(cnt.begin(), cnt.end() - 1);
     for (int64_t q = 0; q < nit; q++) items[fill[cam_of(q)]++] = (int32_t)q;  // codes ascend inside an image
+    cam_items_host = items;
     // widest image: active columns + r, padded to blocks of 4
     int maxact = 0;
     for (int t = 0; t < v.T; t++) {
@@ -333,6 +336,19 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
     s->cam_fast = !any_x && !(ev && ev[0] == '1');
     if (s->cam_fast) {
       MVBA_CUDA(s->camQ.alloc((size_t)std::max(v.C, 1) * MVBA_CAMQ_N));
+      {  // the camera-major block list once more, as 16-byte records the kernel reads coalesced
+        std::vector<TSlot> rec(cam_items_host.size());
+        for (size_t i = 0; i < cam_items_host.size(); i++) {
+          const int64_t code = cam_items_host[i];
+          TSlot sl{};
+          if (code < v.N) { sl.a = h->opid[code]; sl.b = 0; sl.px = h->opix[2 * (size_t)code]; sl.py = h->opix[2 * (size_t)code + 1]; }
+          else if (code < v.N + v.n_dtri) { sl.a = (int32_t)(code - v.N); sl.b = 1u << 24; }
+          else { sl.a = (int32_t)(code - v.N - v.n_dtri); sl.b = 2u << 24; }
+          rec[i] = sl;
+        }
+        if (rec.empty()) rec.push_back(TSlot{});
+        MVBA_CUDA(s->crec.upload(rec));
+      }
       int occ_q = 1;
       MVBA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_q, camq_kernel, 256, 0));
       s->grid_camq = std::max(1, std::min(s->nchunks, h->sm_count * std::max(occ_q, 1)));

@@ -37,7 +37,7 @@ inline int run_build(mvba_problem* h, const mvba_solve_options& o, double radius
     MVBA_CUDA(s->camQ.zero(h->stream));
     CamQArgs qa{};
     qa.x = h->d_x.p; qa.tab = h->d_tab.p; qa.dtab = h->d_dtab.p;
-    qa.chunk_cam = s->chunk_cam.p; qa.chunk_beg = s->chunk_beg.p; qa.citems = s->citems.p; qa.nchunks = s->nchunks; qa.Q = s->camQ.p;
+    qa.chunk_cam = s->chunk_cam.p; qa.chunk_beg = s->chunk_beg.p; qa.citems = s->citems.p; qa.crec = s->crec.p; qa.nchunks = s->nchunks; qa.Q = s->camQ.p;
     camq_kernel<<<s->grid_camq, 256, 0, h->stream>>>(v, qa);
     CamFoldArgs fa{};
     fa.tab = h->d_tab.p; fa.coef = h->d_coef.p; fa.Q = s->camQ.p; fa.jscale_f = a.jscale_f; fa.mode = mode;
@@ -52,7 +52,7 @@ inline int run_build(mvba_problem* h, const mvba_solve_options& o, double radius
     h->launches++;
   }
   if (v.P > 0 && mode == 1) {  // column norms: diag(E'E) per landmark
-    build_kernel<<<s->grid_build, 32 * s->wpb_build, s->smem_build, h->stream>>>(v, a, s->R);
+    colnorm_e_kernel<<<s->grid_backsub, 128, 0, h->stream>>>(v, h->d_x.p, h->d_tab.p, h->d_dtab.p, s->diagE.p);
     h->launches++;
   } else if (v.P > 0) {  // pass B: landmark blocks, Schur elimination
     if (s->ntiles > 0 && s->tile2) {  // staged variant: per-round blobs by bulk copy, two CTAs per SM, dynamic tile queue
@@ -256,7 +256,7 @@ inline int solver_solve(mvba_problem* h, const mvba_solve_options& o, mvba_summa
     if (ne) { jscale_kernel<<<(unsigned)((ne + tb - 1) / tb), tb, 0, h->stream>>>(ne, s->diagE.p, s->jscale_e.p); h->launches++; }
     tm.end();
   }
-  LmOpts lo{o.min_relative_decrease, o.parameter_tolerance, o.function_tolerance, o.max_trust_region_radius, o.min_trust_region_radius};
+  LmOpts lo{o.min_relative_decrease, o.parameter_tolerance, o.function_tolerance, o.max_trust_region_radius, o.min_trust_region_radius, o.gradient_tolerance};
   bool have_cost = false;
   while (iter < o.max_num_iterations) {
     iter++;
@@ -334,11 +334,14 @@ inline int solver_solve(mvba_problem* h, const mvba_solve_options& o, mvba_summa
     int dev_term = rec.linear_iterations;
     rec.linear_iterations = cgit;
     radius = rec.radius; cost = rec.cost; gmax = rec.gradient_max_norm;
+    if (dev_term == 3) {  // gradient tolerance met at the point the previous step reached: this pass over the loop was no iteration
+      iter--; nlin -= cgit; term = MVBA_TERM_CONVERGENCE; break;
+    }
     if (rec.step_accepted) nsucc++;
     if (its && iter < max_its) its[iter] = rec;
     if (o.verbose) std::printf("%4d  %.6e   %9.2e    %.2e   %.2e  %9.2e  %.2e   %6d %s\n", iter, rec.cost, rec.cost_change, rec.gradient_max_norm,
                                rec.step_norm, rec.relative_decrease, rec.radius, cgit, rec.step_accepted ? "" : "(rejected)");
-    if (dev_term) { term = MVBA_TERM_CONVERGENCE; break; }
+    if (dev_term) { term = dev_term == 5 ? MVBA_TERM_FAILURE : MVBA_TERM_CONVERGENCE; break; }
   }
   // gradient tolerance at the final point is checked by the next build in Ceres; the reference's
   // 1e-16 tolerance is never reached in practice, so the last recorded norm is reported.

@@ -12,6 +12,7 @@
 // fit).
 #pragma once
 #include <cmath>
+#include <cstdint>
 #include <stdexcept>
 #include <vector>
 
@@ -126,6 +127,15 @@ class CameraParameters {
     }
   }
   const std::vector<double>& GetDistortion() const { return distortion_coeffs_; }
+  // camera_params.cc:214-254: re-fit the undistortion half of an RPC model from its distortion half (fitRpcUndist,
+  // rpc_distortion.cc:658-719: 400 x 400 samples, 100 LM iterations per degree, parameter tolerance 1e-12).  The fit itself
+  // runs on the device: the entry point mvba_rpc_fit (include/mvba.h) is registered once with SetRpcFitter, so that this
+  // header keeps no link-time dependency on libmvba.so.  Defined in rpc_pairs.h (needs the sample-pair generator).
+  typedef int (*RpcFitter)(int32_t device, int64_t n, const double* in_xy, const double* out_xy, int32_t rpc_degree, int32_t num_iterations,
+                           double parameter_tolerance, int32_t jacobian_mode, double* coeffs, double stats[4]);
+  static RpcFitter& rpc_fitter() { static RpcFitter f = nullptr; return f; }
+  static void SetRpcFitter(RpcFitter f) { rpc_fitter() = f; }
+  inline void updateRpcUndistortion(int num_threads);
   // RPCLensDistortion::set_can_undistort (rig_calibrator.cc:1601-1605): undistortion is refused until the model is re-fitted
   void set_can_undistort(bool v) { can_undistort_ = v; }
 

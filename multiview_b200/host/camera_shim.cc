@@ -154,4 +154,20 @@ int mvh_residual_stats(long long num_blocks, const int* kind, const long long* r
     return (int)st.size();
   } catch (const std::exception& e) { g_cam_err = e.what(); return -1; }
 }
+// CameraParameters::updateRpcUndistortion through a caller-supplied fitter (the address of mvba_rpc_fit, or of the oracle's
+// oracle_rpc_fit in tests): dist[nd] is updated in place (undistortion half); returns 0, -1 on error
+int mvh_update_rpc_undistortion(const int* size, const double* focal, const double* center, double* dist, int nd, const int* undist_size,
+                                const int* crop_size, void* fitter) {
+  try {
+    using namespace camera;
+    CameraParameters cp(Vector2i(size[0], size[1]), Vector2d(focal[0], focal[1]), Vector2d(center[0], center[1]), std::vector<double>(dist, dist + nd));
+    if (undist_size) cp.SetUndistortedSize(Vector2i(undist_size[0], undist_size[1]));
+    if (crop_size) cp.SetDistortedCropSize(Vector2i(crop_size[0], crop_size[1]));
+    CameraParameters::SetRpcFitter(reinterpret_cast<CameraParameters::RpcFitter>(fitter));
+    cp.updateRpcUndistortion(1);
+    const std::vector<double>& d = cp.GetDistortion();
+    for (int i = 0; i < nd; i++) dist[i] = d[(size_t)i];
+    return 0;
+  } catch (const std::exception& e) { g_cam_err = e.what(); return -1; }
+}
 }

@@ -29,3 +29,28 @@ inline void gen_undist_dist_pairs(int num_samples, const camera::CameraParameter
 }
 
 }  // namespace mvba_host
+
+// CameraParameters::updateRpcUndistortion (camera_params.cc:214-254 -> fitRpcUndist, rpc_distortion.cc:658-719): samples of the
+// undistorted image pushed through the RPC DISTORTION half, then an RPC of the same degree is fitted the other way round
+// (distorted -> undistorted) on the device and stored as the second half of the coefficient vector.  num_threads is the
+// reference's Ceres thread count and has no meaning here.
+inline void camera::CameraParameters::updateRpcUndistortion(int /*num_threads*/) {
+  const int num_samples = 400, num_iterations = 100;
+  const double parameter_tolerance = 1e-12;
+  if (distortion_coeffs_.size() % 2 != 0) throw std::runtime_error("Must have an even number of RPC distortion coefficients.");
+  if (!rpc_fitter()) throw std::runtime_error("updateRpcUndistortion: no RPC fitter registered (CameraParameters::SetRpcFitter(mvba_rpc_fit))");
+  const int num_dist = (int)distortion_coeffs_.size() / 2;
+  const int deg = rpc_degree(num_dist);
+  std::vector<double> undist, dist;
+  mvba_host::gen_undist_dist_pairs(num_samples, *this, &undist, &dist);
+  for (size_t i = 0; i + 1 < undist.size(); i += 2) {  // the pairs of the fit: RPC distortion of the centred undistorted sample
+    const Vector2d d = compute_rpc(Vector2d(undist[i], undist[i + 1]), distortion_coeffs_.data(), num_dist);
+    dist[i] = d[0]; dist[i + 1] = d[1];
+  }
+  std::vector<double> coeffs((size_t)num_dist, 0.0);
+  double stats[4] = {0, 0, 0, 0};
+  const int rc = rpc_fitter()(0, (int64_t)(undist.size() / 2), dist.data(), undist.data(), deg, num_iterations, parameter_tolerance, 0, coeffs.data(), stats);
+  if (rc != 0) throw std::runtime_error("updateRpcUndistortion: the device RPC fit failed (code " + std::to_string(rc) + ")");
+  for (int i = 0; i < num_dist; i++) distortion_coeffs_[(size_t)num_dist + i] = coeffs[(size_t)i];
+  can_undistort_ = true;
+}

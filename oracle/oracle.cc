@@ -659,6 +659,7 @@ static int solve(Problem& P, const mvba_solve_options& o, mvba_summary* S, mvba_
   if (its && max_its > 0) { its[0] = mvba_iteration{cost, 0, gmax, 0, 0, radius, 0, 1}; }
   if (gmax <= o.gradient_tolerance) term = MVBA_TERM_CONVERGENCE;
   std::vector<double> rhs(nf), df(nf), de(ne), xf2, xe2;
+  int invalid_steps = 0;
   while (term == MVBA_TERM_NO_CONVERGENCE && iter < o.max_num_iterations) {
     iter++;
     sv.col_sqnorm(cf, ce);
@@ -694,7 +695,9 @@ static int solve(Problem& P, const mvba_solve_options& o, mvba_summary* S, mvba_
     double cost_change = 0, rel = 0, step_norm = 0;
     if (!(mcc > 0) || !std::isfinite(mcc)) {
       radius /= decrease; decrease *= 2;  // invalid step
+      if (++invalid_steps >= 5) { term = MVBA_TERM_FAILURE; }  // max_num_consecutive_invalid_steps, Ceres default
     } else {
+      invalid_steps = 0;
       xf2 = xf; xe2 = xe;
       double sn = 0, xn = 0;
       for (int i = 0; i < nf; i++) { double d = df[i] * sv.scale_f[i]; xf2[i] += d; sn += d * d; xn += xf[i] * xf[i]; }

