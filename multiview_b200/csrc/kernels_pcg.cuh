@@ -284,17 +284,21 @@ __global__ void pcg_check_kernel(PcgScal sc, int it, int refreshed, double eta, 
 // The reduced system (a few MB) stays L2 resident throughout.
 
 // Row w of S x as spmv_row, returning this lane's share of x'(S x).
-__device__ __forceinline__ double spmv_row_dot(const Reduced& S, const Bsr& A, const double* x, double* y, int w, int lane) {
+// (z != null: x is the PREVIOUS direction and the vector multiplied is p = z + beta x, formed on the fly by every reader with the
+// same fused multiply-add; the owner of a row also stores its part of p to pn.  This folds Ceres' direction update into the
+// product and saves one grid barrier per CG iteration without changing a single rounding.)
+__device__ __forceinline__ double pcg_dir(const double* z, const double* x, double beta, int i) { return z ? fma(beta, x[i], z[i]) : x[i]; }
+__device__ __forceinline__ double spmv_row_dot(const Reduced& S, const Bsr& A, const double* x, double* y, int w, int lane,
+                                               const double* z = nullptr, double beta = 0.0, double* pn = nullptr) {
   const int B = S.B;
   double dot = 0;
   if (w < A.nb) {
     double acc[7] = {0, 0, 0, 0, 0, 0, 0};
     for (int e = A.row_ptr[w] + lane; e < A.row_ptr[w + 1]; e += 32) {
       const int c = A.col[e], sl = A.slot[e];
-      const double* xb = x + 7 * c;
       double xv[7];
 #pragma unroll
-      for (int k = 0; k < 7; k++) xv[k] = xb[k];
+      for (int k = 0; k < 7; k++) xv[k] = pcg_dir(z, x, beta, 7 * c + k);
       if (sl >= 0) {
         const double* M = S.Spp + (size_t)sl * 49;
 #pragma unroll
@@ -311,9 +315,9 @@ __device__ __forceinline__ double spmv_row_dot(const Reduced& S, const Bsr& A, c
     }
     double xr[7];
 #pragma unroll
-    for (int r = 0; r < 7; r++) xr[r] = x[7 * w + r];
+    for (int r = 0; r < 7; r++) xr[r] = pcg_dir(z, x, beta, 7 * w + r);
     for (int b = lane; b < B; b += 32) {
-      const double xb = x[S.npc + b];
+      const double xb = pcg_dir(z, x, beta, S.npc + b);
       double t = 0;
 #pragma unroll
       for (int r = 0; r < 7; r++) { const double s = S.Spb[(size_t)(7 * w + r) * B + b]; acc[r] += s * xb; t += s * xr[r]; }
@@ -324,15 +328,15 @@ __device__ __forceinline__ double spmv_row_dot(const Reduced& S, const Bsr& A, c
     for (int r = 0; r < 7; r++) acc[r] = warp_sum(acc[r]);
     if (lane == 0) {
 #pragma unroll
-      for (int r = 0; r < 7; r++) { y[7 * w + r] = acc[r]; dot += xr[r] * acc[r]; }
+      for (int r = 0; r < 7; r++) { y[7 * w + r] = acc[r]; dot += xr[r] * acc[r]; if (pn) pn[7 * w + r] = xr[r]; }
     }
   } else {
     const int b = w - A.nb;
     if (b < B) {
       double t = 0;
-      for (int c = lane; c < B; c += 32) t += S.Sbb[(size_t)b * B + c] * x[S.npc + c];
+      for (int c = lane; c < B; c += 32) t += S.Sbb[(size_t)b * B + c] * pcg_dir(z, x, beta, S.npc + c);
       t = warp_sum(t);
-      if (lane == 0) { atomicAdd(y + S.npc + b, t); dot += x[S.npc + b] * t; }
+      if (lane == 0) { const double xo = pcg_dir(z, x, beta, S.npc + b); atomicAdd(y + S.npc + b, t); dot += xo * t; if (pn) pn[S.npc + b] = xo; }
     }
   }
   return dot;
@@ -344,16 +348,16 @@ __device__ __forceinline__ double spmv_row_dot(const Reduced& S, const Bsr& A, c
 // the one of spmv_row_dot, term for term).  sm_pp: blocks of entries [e0, ...), 49 doubles each; sm_pb: rows 7 r0 ... of S_pb.
 template <bool DOT>
 __device__ __forceinline__ double spmv_row_sm(const Reduced& S, const Bsr& A, const double* sm_pp, const double* sm_pb, int e0, int r0,
-                                              const double* x, double* y, int w, int lane) {
+                                              const double* x, double* y, int w, int lane,
+                                              const double* z = nullptr, double beta = 0.0, double* pn = nullptr) {
   const int B = S.B;
   double dot = 0;
   double acc[7] = {0, 0, 0, 0, 0, 0, 0};
   for (int e = A.row_ptr[w] + lane; e < A.row_ptr[w + 1]; e += 32) {
     const int c = A.col[e];
-    const double* xb = x + 7 * c;
     double xv[7];
 #pragma unroll
-    for (int k = 0; k < 7; k++) xv[k] = xb[k];
+    for (int k = 0; k < 7; k++) xv[k] = pcg_dir(z, x, beta, 7 * c + k);
     const double* M = sm_pp + (size_t)(e - e0) * 49;
 #pragma unroll
     for (int r = 0; r < 7; r++)
@@ -362,9 +366,9 @@ __device__ __forceinline__ double spmv_row_sm(const Reduced& S, const Bsr& A, co
   }
   double xr[7];
 #pragma unroll
-  for (int r = 0; r < 7; r++) xr[r] = x[7 * w + r];
+  for (int r = 0; r < 7; r++) xr[r] = pcg_dir(z, x, beta, 7 * w + r);
   for (int b = lane; b < B; b += 32) {
-    const double xb = x[S.npc + b];
+    const double xb = pcg_dir(z, x, beta, S.npc + b);
     double t = 0;
 #pragma unroll
     for (int r = 0; r < 7; r++) { const double s = sm_pb[(size_t)(7 * (w - r0) + r) * B + b]; acc[r] += s * xb; t += s * xr[r]; }
@@ -375,14 +379,14 @@ __device__ __forceinline__ double spmv_row_sm(const Reduced& S, const Bsr& A, co
   for (int r = 0; r < 7; r++) acc[r] = warp_sum(acc[r]);
   if (lane == 0) {
 #pragma unroll
-    for (int r = 0; r < 7; r++) { y[7 * w + r] = acc[r]; if (DOT) dot += xr[r] * acc[r]; }
+    for (int r = 0; r < 7; r++) { y[7 * w + r] = acc[r]; if (DOT) dot += xr[r] * acc[r]; if (pn) pn[7 * w + r] = xr[r]; }
   }
   return dot;
 }
 
 __global__ void __launch_bounds__(512) pcg_fused_kernel(Reduced S, Bsr A, const double* Mpp, const double* Mbb, const double* b, double* x,
                                                          double* r, double* z, double* p, double* q, PcgScal sc, double eta, int min_it,
-                                                         int max_it, int rows_per_cta) {
+                                                         int max_it, int rows_per_cta, double* p2) {
   namespace cg = cooperative_groups;
   cg::grid_group grid = cg::this_grid();
   const int nf = S.nf, npc = S.npc, B = S.B, nb = S.nb;
@@ -406,7 +410,9 @@ __global__ void __launch_bounds__(512) pcg_fused_kernel(Reduced S, Bsr A, const 
     double* pb = pcg_sm + (size_t)(e1 - e0) * 49;
     for (int i = threadIdx.x; i < 7 * (r1 - r0) * B; i += blockDim.x) pb[i] = S.Spb[(size_t)7 * r0 * B + i];
   }
-  for (int i = gtid; i < nf; i += nthr) { x[i] = 0; r[i] = b[i]; }
+  // two direction buffers: po holds the current p, pn receives the next one inside the product (no separate update pass)
+  double* po = p; double* pn = p2;
+  for (int i = gtid; i < nf; i += nthr) { x[i] = 0; r[i] = b[i]; po[i] = 0; pn[i] = 0; if (i >= npc) q[i] = 0; }
   grid.sync();
   int done = 0, it_done = 0;
   double Q0 = 0.0, alpha = 0.0;
@@ -422,7 +428,7 @@ __global__ void __launch_bounds__(512) pcg_fused_kernel(Reduced S, Bsr A, const 
       if (act) {
         ri = r[i];
         if (pending) {
-          const double xi = x[i] + alpha * p[i];
+          const double xi = x[i] + alpha * po[i];
           ri -= alpha * q[i];
           x[i] = xi; r[i] = ri;
           vq += -xi * (b[i] + ri);
@@ -440,10 +446,11 @@ __global__ void __launch_bounds__(512) pcg_fused_kernel(Reduced S, Bsr A, const 
       for (int bb = lane; bb < B; bb += 32) {
         const int i = npc + bb;
         if (pending) {
-          const double xi = x[i] + alpha * p[i], ri = r[i] - alpha * q[i];
+          const double xi = x[i] + alpha * po[i], ri = r[i] - alpha * q[i];
           x[i] = xi; r[i] = ri;
           vq += -xi * (b[i] + ri);
         }
+        q[i] = 0;  // the border rows of q are completed with atomics in the product below
       }
       __syncwarp();
       for (int bb = lane; bb < B; bb += 32) {
@@ -469,26 +476,25 @@ __global__ void __launch_bounds__(512) pcg_fused_kernel(Reduced S, Bsr A, const 
     const double rho = sc.it[4 * it];
     if (rho == 0.0 || !isfinite(rho)) { done = 2; break; }
     const double beta = (it == 1) ? 0.0 : rho / sc.it[4 * (it - 1)];
-    for (int i = gtid; i < nf; i += nthr) { p[i] = z[i] + beta * p[i]; if (i >= npc) q[i] = 0; }
-    grid.sync();
-    // ---- S: q = S p and p.q ----
+    // ---- S: p = z + beta p (formed by every reader, stored by the row's owner), q = S p and p.q ----
     {
       double v = 0;
       if (rows_per_cta > 0) {
-        for (int w = r0 + wib; w < r1; w += nwib) v += spmv_row_sm<true>(S, A, sm_pp, sm_pb, e0, r0, p, q, w, lane);
-        if (blockIdx.x == gridDim.x - 1) for (int w = nb + wib; w < nb + B; w += nwib) v += spmv_row_dot(S, A, p, q, w, lane);
+        for (int w = r0 + wib; w < r1; w += nwib) v += spmv_row_sm<true>(S, A, sm_pp, sm_pb, e0, r0, po, q, w, lane, z, beta, pn);
+        if (blockIdx.x == gridDim.x - 1) for (int w = nb + wib; w < nb + B; w += nwib) v += spmv_row_dot(S, A, po, q, w, lane, z, beta, pn);
       } else {
-        for (int w = gwarp; w < nb + B; w += nwarp) v += spmv_row_dot(S, A, p, q, w, lane);
+        for (int w = gwarp; w < nb + B; w += nwarp) v += spmv_row_dot(S, A, po, q, w, lane, z, beta, pn);
       }
       block_accumulate(v, sc.it + 4 * it + 1);
     }
     grid.sync();
+    { double* t = po; po = pn; pn = t; }
     const double pq = sc.it[4 * it + 1];
     if (pq <= 0.0 || !isfinite(pq)) { done = 3; break; }  // "matrix is indefinite": keep the last iterate
     alpha = rho / pq;
     pending = true;
     if (it % 10 == 0) {  // residual_reset_period: x updated now, r = b - S x, Q recomputed from it
-      for (int i = gtid; i < nf; i += nthr) { x[i] += alpha * p[i]; if (i >= npc) q[i] = 0; }
+      for (int i = gtid; i < nf; i += nthr) { x[i] += alpha * po[i]; if (i >= npc) q[i] = 0; }
       grid.sync();
       if (rows_per_cta > 0) {
         for (int w = r0 + wib; w < r1; w += nwib) spmv_row_sm<false>(S, A, sm_pp, sm_pb, e0, r0, x, q, w, lane);
@@ -498,7 +504,7 @@ __global__ void __launch_bounds__(512) pcg_fused_kernel(Reduced S, Bsr A, const 
       }
       grid.sync();
       double v = 0;
-      for (int i = gtid; i < nf; i += nthr) { const double ri = b[i] - q[i]; r[i] = ri; v += -x[i] * (b[i] + ri); }
+      for (int i = gtid; i < nf; i += nthr) { const double ri = b[i] - q[i]; r[i] = ri; v += -x[i] * (b[i] + ri); if (i >= npc) q[i] = 0; }
       block_accumulate(v, sc.it + 4 * it + 2);
       pending = false;
       grid.sync();

@@ -105,7 +105,7 @@ struct Solver {
   DBuf<double> red;  // [Spp | Spb | Sbb | Fpp | Fbb | g | diagF | rhs | cost]  (one allreduce)
   size_t o_Spp = 0, o_Spb = 0, o_Sbb = 0, o_Fpp = 0, o_Fbb = 0, o_g = 0, o_diagF = 0, o_rhs = 0, o_cost = 0, o_gmaxe = 0, red_n = 0;
   DBuf<double> Dsq, Mpp, Mbb, work, jscale_f, jscale_e, Hinv, ge, diagE, lo, hi;
-  DBuf<double> y, r, z, p, q, ye, lm, pcg_scal;
+  DBuf<double> y, r, z, p, p2, q, ye, lm, pcg_scal;
   DBuf<int> pcg_flags;
   DBuf<CamDir> camdir;
   DBuf<SensDir> sensdir;
@@ -253,7 +253,7 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
   MVBA_CUDA(s->jscale_f.alloc(nf)); MVBA_CUDA(s->jscale_e.alloc((size_t)3 * std::max(v.P, 1)));
   MVBA_CUDA(s->Hinv.alloc((size_t)6 * std::max(v.P, 1))); MVBA_CUDA(s->ge.alloc((size_t)3 * std::max(v.P, 1)));
   MVBA_CUDA(s->diagE.alloc((size_t)3 * std::max(v.P, 1))); MVBA_CUDA(s->ye.alloc((size_t)3 * std::max(v.P, 1)));
-  MVBA_CUDA(s->y.alloc(nf)); MVBA_CUDA(s->r.alloc(nf)); MVBA_CUDA(s->z.alloc(nf)); MVBA_CUDA(s->p.alloc(nf)); MVBA_CUDA(s->q.alloc(nf));
+  MVBA_CUDA(s->y.alloc(nf)); MVBA_CUDA(s->r.alloc(nf)); MVBA_CUDA(s->z.alloc(nf)); MVBA_CUDA(s->p.alloc(nf)); MVBA_CUDA(s->p2.alloc(nf)); MVBA_CUDA(s->q.alloc(nf));
   MVBA_CUDA(s->lm.alloc(LM_NSLOTS)); MVBA_CUDA(s->pcg_flags.alloc(4));
   MVBA_CUDA(cudaMallocHost((void**)&s->rec, sizeof(mvba_iteration)));
   MVBA_CUDA(cudaMallocHost((void**)&s->flags_host, 4 * sizeof(int)));

@@ -139,7 +139,8 @@ inline int run_pcg(mvba_problem* h, const mvba_solve_options& o, int* iters_out)
     double *xx = s->y.p, *rr = s->r.p, *zz = s->z.p, *pp = s->p.p, *qq = s->q.p;
     double eta = o.eta; int min_it = o.min_linear_solver_iterations, mx = max_it;
     int rpc = s->pcg_rows_per_cta;
-    void* args[] = {&s->R, &s->A, &Mpp, &Mbb, &bb, &xx, &rr, &zz, &pp, &qq, &sc, &eta, &min_it, &mx, &rpc};
+    double* pp2 = s->p2.p;
+    void* args[] = {&s->R, &s->A, &Mpp, &Mbb, &bb, &xx, &rr, &zz, &pp, &qq, &sc, &eta, &min_it, &mx, &rpc, &pp2};
     MVBA_CUDA(cudaLaunchCooperativeKernel((const void*)pcg_fused_kernel, dim3(s->pcg_coop_grid), dim3(s->pcg_threads), args, s->smem_pcg, h->stream));
     h->launches++;
     // the iteration count lands in pinned memory; the caller reads it after the LM iteration's own synchronisation (-1: deferred)
