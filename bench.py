@@ -124,6 +124,7 @@ CPU_SAMPLE = {1: 1.0, 2: 1.0, 3: 1.0, 4: 0.25, 5: 0.25}   # default fraction of 
 def _oracle_solve(pr, iters, jac_mode, cores):
     """One oracle solve; returns (summary, seconds of the LM loop incl. every linearisation, seconds of one-time structure set-up)."""
     from multiview_b200 import _abi
+    import oracle.binding  # noqa: F401  the checker's binding (cpu_baseline / reference arm only)
     lib = C.CDLL(os.path.join(ROOT, "oracle", "liboracle.so"))
     b = _abi.Binding(lib, "oracle_", pr)
     t0 = time.time()

@@ -1,5 +1,6 @@
 """ctypes mirror of include/mvba.h.  The same structs are accepted by libmvba.so (the product) and
-by oracle/liboracle.so (the checker, prefix ``oracle_``), so one binder serves both."""
+by the CPU checker of the tests (oracle/liboracle.so, prefix ``oracle_``): its binding lives under oracle/ (oracle/binding.py,
+test infrastructure) and plugs in through register_checker(); nothing in this package names or loads the checker."""
 from __future__ import annotations
 
 import ctypes as C
@@ -91,13 +92,7 @@ class Binding:
         T = len(pr.sensors)
         cfg = Config(T, len(pr.ref_stamps), len(pr.cam_sensor), pr.num_landmarks, int(pr.no_rig), int(pr.affine_depth),
                      pr.robust_threshold, pr.depth_tri_weight, pr.depth_mesh_weight)
-        if prefix == "mvba_":
-            h = C.c_void_p()
-            self._ck(lib.mvba_create(C.byref(cfg), int(device), C.byref(h)))
-            self.h = h
-        else:
-            lib.oracle_create.restype = C.c_void_p
-            self.h = C.c_void_p(lib.oracle_create(C.byref(cfg)))
+        self._create(cfg, device)
         f = self._f
         for t, s in enumerate(pr.sensors):
             self._ck(f("set_sensor")(self.h, C.c_int32(t), C.c_double(s.width), C.c_double(s.height), C.c_int32(s.nd)))
@@ -121,6 +116,19 @@ class Binding:
                       _p(pr.float_d2i, c_u8_p), _p(pr.float_poses, c_u8_p), int(pr.float_offsets), int(pr.float_scale))
         self._keep.append(m)
         self._ck(f("set_float_mask")(self.h, C.byref(m)))
+
+    def __new__(cls, lib, prefix="mvba_", *args, **kw):
+        # a prefix other than the product's selects a registered checker binding (a subclass; the tests register the CPU oracle's)
+        if cls is Binding and prefix != "mvba_":
+            if prefix not in _CHECKERS:
+                raise MvbaError(f"no binding registered for prefix {prefix!r} (the tests register the CPU checker: oracle/binding.py)")
+            return object.__new__(_CHECKERS[prefix])
+        return object.__new__(cls)
+
+    def _create(self, cfg, device):
+        h = C.c_void_p()
+        self._ck(self.lib.mvba_create(C.byref(cfg), int(device), C.byref(h)))
+        self.h = h
 
     def _f(self, name):
         return getattr(self.lib, self.prefix + name)
@@ -172,13 +180,11 @@ class Binding:
         W = self.jacobian_width(kind)
         rows = 2 if kind == 0 else 3
         r = np.zeros((count, rows)); J = np.zeros((count, rows, W))
-        if self.prefix == "mvba_":
-            self._ck(self.lib.mvba_evaluate_jacobian(self.h, C.c_int32(kind), C.c_int64(first), C.c_int64(count),
-                                                     _p(r, c_double_p), _p(J, c_double_p)))
-        else:
-            self._ck(self.lib.oracle_evaluate_jacobian(self.h, C.c_int32(kind), C.c_int64(first), C.c_int64(count), C.c_int32(mode),
-                                                       _p(r, c_double_p), _p(J, c_double_p)))
+        self._evaluate_jacobian(kind, first, count, mode, r, J)
         return r, J
+
+    def _evaluate_jacobian(self, kind, first, count, mode, r, J):
+        self._ck(self.lib.mvba_evaluate_jacobian(self.h, C.c_int32(kind), C.c_int64(first), C.c_int64(count), _p(r, c_double_p), _p(J, c_double_p)))
 
     # -- per-track steps around a pass (N1, N2) ------------------------------------------
     def triangulate(self, inlier=None, xyz0=None):
@@ -226,14 +232,25 @@ class Binding:
         o = options or default_options()
         s = Summary()
         its = (Iteration * max_log)()
-        if self.prefix == "mvba_":
-            self._ck(self.lib.mvba_solve(self.h, C.byref(o), C.byref(s), its, C.c_int32(max_log)))
-        else:
-            self._ck(self.lib.oracle_solve(self.h, C.byref(o), C.byref(s), its, C.c_int32(max_log), C.c_int32(jac_mode),
-                                           C.c_int32(num_threads)))
+        self._solve(o, s, its, max_log, jac_mode, num_threads)
         n = min(max_log, s.num_iterations + 1)
         log = [{k: getattr(its[i], k) for k, _ in Iteration._fields_} for i in range(n)]
         return s, log
+
+
+    def _solve(self, o, s, its, max_log, jac_mode, num_threads):
+        self._ck(self.lib.mvba_solve(self.h, C.byref(o), C.byref(s), its, C.c_int32(max_log)))
+
+
+_CHECKERS = {}      # prefix -> Binding subclass
+_RPC_FITTERS = {}   # prefix -> function(lib, a, b, deg, num_iterations, parameter_tolerance, num_threads, c, st) -> rc
+
+
+def register_checker(prefix, binding_cls, rpc_fit_fn=None):
+    """Test infrastructure hook: a library with another symbol prefix (the CPU oracle) binds through its own subclass."""
+    _CHECKERS[prefix] = binding_cls
+    if rpc_fit_fn is not None:
+        _RPC_FITTERS[prefix] = rpc_fit_fn
 
 
 _LIB = None
@@ -260,7 +277,7 @@ def rpc_num_params(deg: int) -> int:
 
 
 def rpc_fit(lib, prefix, in_xy, out_xy, deg, num_iterations=100, parameter_tolerance=1e-12, jacobian_mode=0, num_threads=0, device=0):
-    """fitRpcDist-style fit of out = rpc(in) through `mvba_rpc_fit` (product) or `oracle_rpc_fit` (checker):
+    """fitRpcDist-style fit of out = rpc(in) through `mvba_rpc_fit` (product) or a registered checker:
     (coeffs, {initial_cost, final_cost, iterations, successful})."""
     a = np.ascontiguousarray(in_xy, np.float64); b = np.ascontiguousarray(out_xy, np.float64)
     assert a.shape == b.shape and a.ndim == 2 and a.shape[1] == 2
@@ -271,17 +288,9 @@ def rpc_fit(lib, prefix, in_xy, out_xy, deg, num_iterations=100, parameter_toler
         if rc != 0:
             raise MvbaError(f"mvba_rpc_fit failed ({rc}): {lib.mvba_last_error().decode()}")
     else:
-        rc = lib.oracle_rpc_fit(C.c_int64(len(a)), _p(a, c_double_p), _p(b, c_double_p), C.c_int32(deg), C.c_int32(num_iterations),
-                                C.c_double(parameter_tolerance), C.c_int32(num_threads), _p(c, c_double_p), _p(st, c_double_p))
+        if prefix not in _RPC_FITTERS:
+            raise MvbaError(f"no RPC fitter registered for prefix {prefix!r}")
+        rc = _RPC_FITTERS[prefix](lib, a, b, deg, num_iterations, parameter_tolerance, num_threads, c, st)
         if rc != 0:
-            raise MvbaError(f"oracle_rpc_fit failed ({rc})")
+            raise MvbaError(f"{prefix}rpc_fit failed ({rc})")
     return c, dict(initial_cost=st[0], final_cost=st[1], iterations=int(st[2]), successful=int(st[3]))
-
-
-def compute_rpc(oracle_lib, pts, coeffs):
-    """compute_rpc (rpc_distortion.cc:116-160) of the oracle at an array of points."""
-    pts = np.ascontiguousarray(pts, np.float64); c = np.ascontiguousarray(coeffs, np.float64)
-    out = np.zeros_like(pts)
-    for i in range(len(pts)):
-        oracle_lib.oracle_compute_rpc(_p(pts[i], c_double_p), _p(c, c_double_p), C.c_int32(len(c)), _p(out[i], c_double_p))
-    return out

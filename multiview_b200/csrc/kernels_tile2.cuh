@@ -24,7 +24,7 @@
 namespace mvba {
 
 #define MVBA_T2_THREADS 256
-#define MVBA_T2_GCAP (MVBA_T2_THREADS - 32)  // gather groups of one round (one thread each, warp 0 inverts)
+#define MVBA_T2_GCAP MVBA_T2_THREADS  // gather groups of one round (one thread each)
 
 struct alignas(16) TRoundHdr { int32_t kc, nit, ngrp, kc_next; uint32_t next_bytes; int32_t pad[3]; };
 static_assert(sizeof(TRoundHdr) == 32, "round blob layout");
@@ -34,13 +34,14 @@ __host__ __device__ inline uint32_t t2_blob_bytes(int kc, int kc_next, int nit, 
   return 32u + t2_align16(8u * kc) + t2_align16(4u * kc_next) + 16u * nit + 16u * ngrp;
 }
 
-// 25 doubles: an ODD stride in 8-byte units, so that the same field of consecutive slots falls in different banks
-// (a 24-double record puts every slot in one of two bank groups: 16-way conflicts on each access)
-struct TRec2 { double M[9], Z[3], y[3], H[6], g[3], pad; };
-static_assert(sizeof(TRec2) == 200, "TRec2 layout");
+// 13 doubles: an ODD stride in 8-byte units, so that the same field of consecutive slots falls in different banks.  What the
+// gather needs of a block: M = (sr A)'E and Z (the rig rotation acts on Z + dl, dl per image); the block's share of E'E and E'r
+// never leaves the registers (it is summed over the track's lanes with shuffles).
+struct TRec2 { double M[9], Z[3], pad; };
+static_assert(sizeof(TRec2) == 104, "TRec2 layout");
 // Where slot q's record lives: one record is skipped after every eight.  Neighbouring gather threads read the records of
-// neighbouring TRACKS, usually eight slots apart: 8 x 25 doubles is 8 (mod 16) -- two bank positions, 16-way conflicts --
-// while 9 x 25 is 1 (mod 16).
+// neighbouring TRACKS, usually eight slots apart: 8 x 13 doubles is 8 (mod 16) -- two bank positions, 16-way conflicts --
+// while 9 x 13 is 5 (mod 16).
 __host__ __device__ inline int t2_rslot(int q) { return q + (q >> 3); }
 __host__ __device__ inline int t2_rcap(int icap) { return icap + (icap >> 3) + 1; }
 
@@ -128,8 +129,8 @@ __device__ __forceinline__ void t2_gather(const int4 raw, const uint16_t* __rest
     double M[9];
 #pragma unroll
     for (int k = 0; k < 9; k++) M[k] = r.M[k];
-    const double* W = role == 2 ? r.y : r.Z;
-    const double W0 = W[0], W1 = W[1], W2 = W[2];
+    double W0 = r.Z[0], W1 = r.Z[1], W2 = r.Z[2];
+    if (role == 2) { W0 += cp->dl[0]; W1 += cp->dl[1]; W2 += cp->dl[2]; }  // the rig rotation acts on Xc - t_rc = Z + (t - t_rc)
     double N[9];  // N[:,b] = W x M[:,b]
 #pragma unroll
     for (int b = 0; b < 3; b++) {
@@ -267,39 +268,41 @@ __global__ void __launch_bounds__(MVBA_T2_THREADS, 2) tile2_kernel(View v, Tile2
       {
         double2* gz = reinterpret_cast<double2*>(Gs);
         const int nz = L8 * KK / 2;
-        for (int i = tid; i < nz; i += NT) gz[i] = make_double2(0.0, 0.0);
+        const int v0 = Lt * KK / 2, v1 = v0 + (3 * kc + 1) / 2;  // row Lt, columns < 3 kc: written by the track heads below, not cleared
+        for (int i = tid; i < nz; i += NT) if (i < v0 || i >= v1) gz[i] = make_double2(0.0, 0.0);
       }
-      if (tid < nit) {
+      double H[6] = {0, 0, 0, 0, 0, 0}, g[3] = {0, 0, 0};  // this block's share of E'E and E'r (zero for padding slots)
+      int my_k = -1;                                          // track slot of this thread's block
+      if (tid < nit && ((slots[tid].b >> 24) & 7) != 7) {
         const TSlot sl = slots[tid];
         const int kind = (sl.b >> 24) & 7, ks = sl.b >> 27, cid = sl.b & 0xffffffu;
+        my_k = ks;
         const double* Xk = Xcur + 6 * ks;
         Item it;
-        double yv[3] = {0, 0, 0};
         if (kind == 0) {
           it.nr = 2; it.loss_a = v.robust_th;
           const double X0 = Xk[0], X1 = Xk[1], X2 = Xk[2];
-          double Rm[9], tv[3], dl[3];
+          double Rm[9], tv[3];
           int sensor;
           if (staged) {
             const CamPack* cp = t2_pack<true>(pack_s, a.pack, cid, c0);
 #pragma unroll
             for (int i = 0; i < 9; i++) Rm[i] = cp->R[i];
 #pragma unroll
-            for (int i = 0; i < 3; i++) { tv[i] = cp->t[i]; dl[i] = cp->dl[i]; }
+            for (int i = 0; i < 3; i++) tv[i] = cp->t[i];
             sensor = cp->sensor;
           } else {
             const CamPack* cp = t2_pack<false>(pack_s, a.pack, cid, c0);
 #pragma unroll
             for (int i = 0; i < 9; i++) Rm[i] = __ldg(cp->R + i);
 #pragma unroll
-            for (int i = 0; i < 3; i++) { tv[i] = __ldg(cp->t + i); dl[i] = __ldg(cp->dl + i); }
+            for (int i = 0; i < 3; i++) tv[i] = __ldg(cp->t + i);
             sensor = __ldg(&cp->sensor);
           }
 #pragma unroll
           for (int i = 0; i < 3; i++) {
             it.Z[i] = Rm[3 * i] * X0 + Rm[3 * i + 1] * X1 + Rm[3 * i + 2] * X2;
             it.Xc[i] = it.Z[i] + tv[i];
-            yv[i] = it.Z[i] + dl[i];
           }
           project_distort<true>(v.sens[sensor], a.b.x, it.Xc, make_float2(sl.px, sl.py), it.r, it.A, it.Jf, &it.Jc, nullptr, nullptr, v.fov_tab + 2 * sensor);
           it.r[2] = 0;
@@ -309,9 +312,6 @@ __global__ void __launch_bounds__(MVBA_T2_THREADS, 2) tile2_kernel(View v, Tile2
             for (int b = 0; b < 3; b++) it.E[3 * i + b] = it.A[3 * i] * Rm[b] + it.A[3 * i + 1] * Rm[3 + b] + it.A[3 * i + 2] * Rm[6 + b];
         } else if (kind <= 2) {
           eval_depth(v, a.b.x, a.b.tab, a.b.dtab, kind == 1 ? MVBA_BLOCK_DEPTH_TRI : MVBA_BLOCK_DEPTH_MESH, sl.a, it);
-          const double* trc = a.b.tab[it.cid].trc;
-#pragma unroll
-          for (int i = 0; i < 3; i++) yv[i] = it.Xc[i] - __ldg(trc + i);
         } else {
           eval_prior(v, a.b.x, sl.a, it);
         }
@@ -325,7 +325,6 @@ __global__ void __launch_bounds__(MVBA_T2_THREADS, 2) tile2_kernel(View v, Tile2
         double Es[9];
 #pragma unroll
         for (int k = 0; k < 9; k++) Es[k] = (k / 3 < it.nr) ? sr * it.E[k] * se[k % 3] : 0.0;
-        double H[6] = {0, 0, 0, 0, 0, 0}, g[3] = {0, 0, 0};
 #pragma unroll
         for (int r = 0; r < 3; r++) {
           const double* e = Es + 3 * r;
@@ -334,14 +333,10 @@ __global__ void __launch_bounds__(MVBA_T2_THREADS, 2) tile2_kernel(View v, Tile2
           g[0] += e[0] * rs; g[1] += e[1] * rs; g[2] += e[2] * rs;
         }
         TRec2& rc = rec[t2_rslot(tid)];
-#pragma unroll
-        for (int k = 0; k < 6; k++) rc.H[k] = H[k];
-#pragma unroll
-        for (int k = 0; k < 3; k++) rc.g[k] = g[k];
         rcid[t2_rslot(tid)] = kind >= 3 ? -1 : cid;
         if (kind < 3) {
 #pragma unroll
-          for (int k = 0; k < 3; k++) { rc.Z[k] = it.Z[k]; rc.y[k] = yv[k]; }
+          for (int k = 0; k < 3; k++) rc.Z[k] = it.Z[k];
 #pragma unroll
           for (int b = 0; b < 3; b++)
 #pragma unroll
@@ -352,28 +347,23 @@ __global__ void __launch_bounds__(MVBA_T2_THREADS, 2) tile2_kernel(View v, Tile2
             }
         }
       }
-      T2PROF(1);
-      __syncthreads();
-      T2PROF(2);
-      // ---- P2: warp 0 sums and inverts the landmark blocks; the other warps gather their group's rows of G = F'E
-      //      (Jacobi-scaled, written to Gs; scaled by L in place after the barrier) ----
-      int g_lcol = 0, g_k = 0, g_rows = 0;
-      if (wib == 0) {
-        if (tid < kc) {
-          const TTrk tk = trk[tid];
-          double H[6] = {0, 0, 0, 0, 0, 0}, gE[3] = {0, 0, 0};
-          // lane k starts at its track's block k mod n: neighbouring lanes (tracks, usually n slots apart) then read records
-          // n + 1 slots apart, an odd multiple of the odd record stride -- no bank conflicts
-          const int rot = tk.n > 0 ? tid % tk.n : 0;
-          for (int i = 0; i < tk.n; i++) {
-            const int ii = i + rot < tk.n ? i + rot : i + rot - tk.n;
-            const TRec2& r = rec[t2_rslot(tk.q0 + ii)];
+      // ---- landmark block of every track: its slots are consecutive lanes of ONE warp (the host pads the slot list so that no
+      //      track straddles a warp), so E'E and E'r are summed with shuffles and the track's first lane factors the block ----
+      {
+        int seg_end = lane + 1;
+        bool head = false;
+        TTrk tk = TTrk{0, 0, 0};
+        if (my_k >= 0) { tk = trk[my_k]; seg_end = tk.q0 + tk.n - (tid - lane); head = tk.q0 == tid; }
 #pragma unroll
-            for (int k = 0; k < 6; k++) H[k] += r.H[k];
+        for (int d = 1; d < 32; d <<= 1) {
+          const bool in = lane + d < seg_end;
 #pragma unroll
-            for (int k = 0; k < 3; k++) gE[k] += r.g[k];
-          }
-          const double ir = 1.0 / a.b.radius;  // warp-uniform
+          for (int k = 0; k < 6; k++) { const double t = __shfl_down_sync(0xffffffffu, H[k], d); if (in) H[k] += t; }
+#pragma unroll
+          for (int k = 0; k < 3; k++) { const double t = __shfl_down_sync(0xffffffffu, g[k], d); if (in) g[k] += t; }
+        }
+        if (head) {
+          const double ir = 1.0 / a.b.radius;
           H[0] += fmin(fmax(H[0], a.b.min_diag), a.b.max_diag) * ir;
           H[3] += fmin(fmax(H[3], a.b.min_diag), a.b.max_diag) * ir;
           H[5] += fmin(fmax(H[5], a.b.min_diag), a.b.max_diag) * ir;
@@ -391,52 +381,45 @@ __global__ void __launch_bounds__(MVBA_T2_THREADS, 2) tile2_kernel(View v, Tile2
 #pragma unroll
           for (int k = 0; k < 6; k++) a.b.Hinv[6 * (size_t)tk.p + k] = Hi[k];
 #pragma unroll
-          for (int k = 0; k < 3; k++) a.b.ge[3 * (size_t)tk.p + k] = gE[k];
-          double* L = Ls + 6 * tid;
+          for (int k = 0; k < 3; k++) a.b.ge[3 * (size_t)tk.p + k] = g[k];
+          double* L = Ls + 6 * my_k;
           L[0] = i00; L[1] = u01; L[2] = i11; L[3] = u02; L[4] = u12; L[5] = i22;
-          double* vr = Gs + (size_t)Lt * KK + 3 * tid;  // v = U' E'r
-          vr[0] = i00 * gE[0];
-          vr[1] = u01 * gE[0] + i11 * gE[1];
-          vr[2] = u02 * gE[0] + u12 * gE[1] + i22 * gE[2];
+          double* vr = Gs + (size_t)Lt * KK + 3 * my_k;  // v = U' E'r
+          vr[0] = i00 * g[0];
+          vr[1] = u01 * g[0] + i11 * g[1];
+          vr[2] = u02 * g[0] + u12 * g[1] + i22 * g[2];
+          if (my_k == kc - 1 && ((3 * kc) & 1)) vr[3] = 0.0;  // the uncleared pair of row Lt ends one column past the last track
         }
-        if (tid < kc_next) t2_fetch_landmark(v, a.b, next_p[tid], Xnext + 6 * tid);
-      } else if (tid - 32 < ngrp) {
-        const int4 raw = gtab[tid - 32];
+      }
+      T2PROF(1);
+      __syncthreads();
+      T2PROF(2);
+      // ---- P2: one thread per (track, parameter block) group gathers its rows of G = F'E and stores Gs = diag(cs) G U ----
+      if (tid < kc_next) t2_fetch_landmark(v, a.b, next_p[tid], Xnext + 6 * tid);  // next round's landmarks, waited for behind P3
+      if (tid < ngrp) {
+        const int4 raw = gtab[tid];
         const bool single = (((unsigned)raw.y >> 24) & 0x80) != 0;
-        g_lcol = raw.y & 0xffff; g_k = (raw.y >> 16) & 0xff; g_rows = single ? 1 : 7;
+        const int g_lcol = raw.y & 0xffff, g_k = (raw.y >> 16) & 0xff, g_rows = single ? 1 : 7;
         double o[7][3];
 #pragma unroll
         for (int r = 0; r < 7; r++) { o[r][0] = 0; o[r][1] = 0; o[r][2] = 0; }
         if (staged) t2_gather<true>(raw, a.con, rec, rcid, pack_s, a.pack, c0, o);
         else t2_gather<false>(raw, a.con, rec, rcid, pack_s, a.pack, c0, o);
+        const double* L = Ls + 6 * g_k;
+        const double u00 = L[0], u01 = L[1], u11 = L[2], u02 = L[3], u12 = L[4], u22 = L[5];
 #pragma unroll
         for (int r = 0; r < 7; r++) {
           if (r < g_rows) {
             const int l = g_lcol + r;
             const double sc = cs[l];
             double* gp = Gs + (size_t)l * KK + 3 * g_k;
-            gp[0] = sc * o[r][0]; gp[1] = sc * o[r][1]; gp[2] = sc * o[r][2];
+            gp[0] = sc * (o[r][0] * u00);
+            gp[1] = sc * (o[r][0] * u01 + o[r][1] * u11);
+            gp[2] = sc * (o[r][0] * u02 + o[r][1] * u12 + o[r][2] * u22);
           }
         }
       }
       T2PROF(3);
-      __syncthreads();
-      T2PROF(4);
-      // ---- Gs = diag(cs) G U, in place (every group owns its 7 x 3 entries) ----
-      if (g_rows > 0) {
-        const double* L = Ls + 6 * g_k;
-        const double u00 = L[0], u01 = L[1], u11 = L[2], u02 = L[3], u12 = L[4], u22 = L[5];
-#pragma unroll
-        for (int r = 0; r < 7; r++) {
-          if (r < g_rows) {
-            double* gp = Gs + (size_t)(g_lcol + r) * KK + 3 * g_k;
-            const double o0 = gp[0], o1 = gp[1], o2 = gp[2];
-            gp[0] = o0 * u00;
-            gp[1] = o0 * u01 + o1 * u11;
-            gp[2] = o0 * u02 + o1 * u12 + o2 * u22;
-          }
-        }
-      }
       __syncthreads();
       T2PROF(5);
       // the round's table is consumed: fetch the next one while the tensor cores run
@@ -464,7 +447,7 @@ __global__ void __launch_bounds__(MVBA_T2_THREADS, 2) tile2_kernel(View v, Tile2
         }
       }
       T2PROF(6);
-      if (wib == 0) cp_async_wait_all();  // the next round's landmarks (fetched during P2) are in place
+      cp_async_wait_all();  // the next round's landmarks (fetched during P2) are in place
       __syncthreads();
       T2PROF(7);
     }

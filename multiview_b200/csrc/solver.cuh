@@ -500,18 +500,22 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
       int ti = t0[t];
       while (ti < t0[t + 1]) {
         int kc = 0, nit = 0, ng = 0;
-        while (ti + kc < t0[t + 1] && kc < s->tile_K && nit + trk_items[order[ti + kc]] <= s->tile_icap) {
+        // staged kernel: the slots of a track must be lanes of one warp (its landmark block is summed with shuffles), so the slot
+        // list is padded to the next multiple of 32 where a track would straddle
+        auto slot_of = [&](int at, int n) { return use_t2 && (at & 31) + n > 32 ? (at + 31) & ~31 : at; };
+        while (ti + kc < t0[t + 1] && kc < s->tile_K && slot_of(nit, trk_items[order[ti + kc]]) + trk_items[order[ti + kc]] <= s->tile_icap) {
           if (use_t2) {  // one gather thread per group: count the track's distinct parameter blocks
             const int n = count_groups(order[ti + kc]);
             if (ng + n > gcap) break;
             ng += n;
           }
-          nit += trk_items[order[ti + kc]]; kc++;
+          nit = slot_of(nit, trk_items[order[ti + kc]]) + trk_items[order[ti + kc]]; kc++;
         }
         if (kc == 0) return fail(MVBA_EINVAL, "mvba: a tile track does not fit the staging buffer");
         int q = 0;
         for (int k = 0; k < kc; k++) {
           const int p = order[ti + k];
+          for (const int q1 = slot_of(q, trk_items[p]); q < q1; q++) blk.push_back(TBlk{0, 7});  // padding slots (kind 7: nothing to evaluate)
           ttrk.push_back(TTrk{p, (int16_t)q, (int16_t)trk_items[p]});
           keys.clear();
           auto contribute = [&](int lcol, int single, int slot, int role) {
@@ -592,6 +596,7 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
           std::memcpy(q, ttrk.data() + round_trk0[r], (size_t)kc * sizeof(TTrk)); q += t2_align16(8u * kc);
           for (int k = 0; k < kn; k++) { const int32_t pn = ttrk[round_trk0[r + 1] + k].p; std::memcpy(q + 4 * k, &pn, 4); }
           q += t2_align16(4u * kn);
+          for (int i = 0; i < nit; i++) { TSlot pad{}; pad.b = 7u << 24; std::memcpy(q + 16 * (size_t)i, &pad, 16); }
           for (int k = 0; k < kc; k++) {
             const TTrk& tk = ttrk[round_trk0[r] + k];
             for (int i = 0; i < tk.n; i++) {

@@ -92,7 +92,7 @@ inline int run_build(mvba_problem* h, const mvba_solve_options& o, double radius
     cudaMemcpyFromSymbol(pr, g_tile_prof, sizeof(pr));
     cudaMemcpyToSymbol(g_tile_prof, z, sizeof(z));
     double tot = 0; for (int i = 0; i < 8; i++) tot += (double)pr[i];
-    std::printf("tile2 prof (thread 0 of each CTA, %% of cycles): prologue+flush %.1f | P1 %.1f | bar %.1f | P2 (inverse, warp 0) %.1f | bar %.1f | scale+bar %.1f | P3 %.1f | bar %.1f  (Mcycles/CTA %.2f)\n",
+    std::printf("tile2 prof (thread 0 of each CTA, %% of cycles): prologue+flush %.1f | P1 + landmark blocks %.1f | bar %.1f | P2 gather %.1f | (unused) %.1f | bar %.1f | P3 %.1f | bar %.1f  (Mcycles/CTA %.2f)\n",
                 100 * pr[0] / tot, 100 * pr[1] / tot, 100 * pr[2] / tot, 100 * pr[3] / tot, 100 * pr[4] / tot, 100 * pr[5] / tot, 100 * pr[6] / tot, 100 * pr[7] / tot,
                 tot / s->grid_tile2 * 1e-6);
     static bool once2 = false;

@@ -12,6 +12,7 @@ import torch.distributed as dist
 import torch.multiprocessing as mp
 
 from multiview_b200 import _abi, synth
+import oracle.binding  # noqa: F401  (spawned workers do not go through conftest.py)
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 CASE = dict(sensors="rig3", num_ref=12, num_landmarks=500, obs_per_track=5, outlier_frac=0.02)

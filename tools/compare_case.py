@@ -5,6 +5,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
 import ctypes as C
 from multiview_b200 import synth, _abi
+import oracle.binding  # noqa: F401
 from test_gpu_parity_solve import CASES
 
 def main():

@@ -3,6 +3,7 @@ import ctypes as C, sys, time, os
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from multiview_b200 import synth, _abi
+import oracle.binding  # noqa: F401
 
 def main():
     cfgs = [int(a) for a in sys.argv[1].split(",")] if len(sys.argv) > 1 else [1, 2, 3, 4]

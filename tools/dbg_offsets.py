@@ -4,6 +4,7 @@ import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
 from multiview_b200 import _abi, synth
+import oracle.binding  # noqa: F401
 from test_gpu_parity_solve import CASES, _param_error
 kw = dict(CASES["offsets"]); kw.update(tri_weight=5.0, tri_robust_threshold=1.0, outlier_frac=0.0)
 pr = synth.make_problem(seed=23, **kw)

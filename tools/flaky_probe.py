@@ -3,6 +3,7 @@ import ctypes as C, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
 from multiview_b200 import synth, _abi
+import oracle.binding  # noqa: F401
 from test_gpu_parity_solve import CASES
 name = sys.argv[1]; reps = int(sys.argv[2]); iters = int(sys.argv[3])
 olib = C.CDLL(os.path.join(_abi.ROOT, "oracle", "liboracle.so")); plib = _abi.load_product()

@@ -12,6 +12,7 @@ import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
 from multiview_b200 import _abi  # noqa: E402
+import oracle.binding  # noqa: F401
 from test_rpc_fit import grid, radtan, rpc_eval  # noqa: E402
 
 ns = int(sys.argv[1]) if len(sys.argv) > 1 else 400
