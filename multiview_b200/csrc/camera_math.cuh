@@ -207,26 +207,26 @@ __device__ __forceinline__ void project_distort(const SensorDev& s, const double
     if (WANT_J) { dpx[0] = f; dpx[1] = 0; dpy[0] = 0; dpy[1] = f; Jf[0] = px; Jf[1] = py; *Jc = 1.0; }
   } else if (s.nd == 1) {
     // FOV model, camera_params.cc:269-281
-    const double w = dist[0];
-    const double ux = f * px, uy = f * py;
-    const double nx = ux / f, ny = uy / f;
+    // (the reference normalises (f p) / f; the quotient is p up to one rounding, and p is used directly)
+    const double nx = px, ny = py;
     const double ru = sqrt(nx * nx + ny * ny);
     const double k = fov[0];             // 2 tan(w / 2), once per sensor and evaluation point (prep_cameras_kernel)
     const double th = 0.5 * k;
     const double at = atan(ru * k);
     const double rd = at * fov[1];       // 1 / w
+    const double iru = 1.0 / ru;
     double conv = 1.0;
-    if (ru > 1e-5) conv = rd / ru;
+    if (ru > 1e-5) conv = rd * iru;
     dx = (cx - hx) + conv * (nx * f) + hx; dy = (cy - hy) + conv * (ny * f) + hy;
     if (WANT_J) {
       double dconv_dru = 0, dconv_dw = 0;
       if (ru > 1e-5) {
-        double den = 1.0 + k * k * ru * ru;
-        dconv_dru = (k * ru / den - at) / (w * ru * ru);
+        const double iden = 1.0 / (1.0 + k * k * ru * ru), iw = fov[1];
+        dconv_dru = (k * ru * iden - at) * (iw * iru * iru);
         double dk = 1.0 + th * th;  // d(2 tan(w/2))/dw
-        dconv_dw = (ru * dk / den) / (w * ru) - at / (w * w * ru);
+        dconv_dw = (dk * iden) * iw - at * (iw * iw * iru);
       }
-      double g = (ru > 0) ? dconv_dru / ru : 0.0;
+      double g = (ru > 0) ? dconv_dru * iru : 0.0;
       dpx[0] = f * (conv + g * nx * nx); dpx[1] = f * g * nx * ny;
       dpy[0] = f * g * nx * ny; dpy[1] = f * (conv + g * ny * ny);
       Jf[0] = conv * nx; Jf[1] = conv * ny; *Jc = 1.0;
@@ -236,8 +236,7 @@ __device__ __forceinline__ void project_distort(const SensorDev& s, const double
     // Tsai / radtan, camera_params.cc:282-308
     const double k1 = dist[0], k2 = dist[1], p1 = dist[2], p2 = dist[3];
     const double k3 = (s.nd == 5) ? dist[4] : 0.0;
-    const double ux = f * px, uy = f * py;
-    const double nx = ux / f, ny = uy / f;
+    const double nx = px, ny = py;  // (f p) / f in the reference
     const double r2 = nx * nx + ny * ny;
     const double rad = 1.0 + k1 * r2 + k2 * r2 * r2 + k3 * r2 * r2 * r2;
     const double ex = rad * nx + (2.0 * p1 * nx * ny + p2 * (r2 + 2.0 * nx * nx));

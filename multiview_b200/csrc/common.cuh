@@ -140,13 +140,13 @@ __device__ __forceinline__ void cauchy(double a, double s, double* half_rho, dou
   double b = a * a;
   double sum = 1.0 + s / b;
   *half_rho = 0.5 * b * log(sum);
-  *sqrt_rho1 = sqrt(1.0 / sum);
+  *sqrt_rho1 = rsqrt(sum);  // sqrt(rho'(s)) = (1 + s / b)^(-1/2): one reciprocal square root instead of a division and a root
 }
 
 // Corrector scale alone (the build needs the cost itself only at the first point of a solve: no logarithm otherwise).
 __device__ __forceinline__ double cauchy_sr(double a, double s) {
   double b = a * a;
-  return sqrt(1.0 / (1.0 + s / b));
+  return rsqrt(1.0 + s / b);
 }
 
 }  // namespace mvba
