@@ -240,3 +240,19 @@ def test_both_sharding_modes_partition_the_tracks(locality, oracle_lib):
         assert max(images) < 0.75 * n_img          # a rank sees only part of the images ...
     else:
         assert min(images) > 0.9 * n_img           # ... while input-order ranges of random tracks see nearly all of them
+
+
+def test_the_product_package_carries_no_checker_code():
+    """The CPU oracle is test infrastructure: nothing under multiview_b200/ may call, link, include or import it (the one
+    hook is _abi.register_checker, which oracle/binding.py calls from the tests' side)."""
+    pkg = os.path.join(ROOT, "multiview_b200")
+    pat = r'oracle_[a-z_]+\s*\(|["\'][^"\'\n]*liboracle|#include\s+"[^"]*oracle|^\s*import oracle|^\s*from oracle'
+    hits = []
+    for d, _, files in os.walk(pkg):
+        for f in files:
+            if not f.endswith((".py", ".cu", ".cuh", ".h", ".cc", ".cpp", "Makefile")):
+                continue
+            txt = open(os.path.join(d, f), errors="replace").read()
+            for m in re.finditer(pat, txt, flags=re.M):
+                hits.append((os.path.relpath(os.path.join(d, f), ROOT), m.group(0)))
+    assert not hits, hits
