@@ -285,6 +285,23 @@ int mvba_mesh_intersect(mvba_problem* h, int64_t num_vertices, const float* vert
 int mvba_rpc_fit(int32_t device, int64_t n, const double* in_xy, const double* out_xy, int32_t rpc_degree,
                  int32_t num_iterations, double parameter_tolerance, int32_t jacobian_mode, double* coeffs, double stats[4]);
 
+/* mvba_rpc_fit for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  NO COUNTERPART IN THE REFERENCE.  Same arguments, same result
+ * and same errors as mvba_rpc_fit, but it allocates nothing: every byte of device scratch (the staged samples, the per-CTA
+ * partial normal equations and their folded sums) lives in one file-scope `static __device__` array of the library, about
+ * 7.1 MB, which every GPU that loads libmvba.so holds until the process exits.  Limits: n <= MVBA_RPC_STATIC_MAX_N samples
+ * (more: MVBA_EINVAL with a message naming the limit; use mvba_rpc_fit), and at most MVBA_RPC_STATIC_MAX_PARTS CTAs
+ * accumulate (the allocating entry point uses up to two per SM; with n <= 64 MVBA_RPC_STATIC_MAX_PARTS both use the same
+ * grid and return identical bits, beyond that the sums are folded in a different order and the fits agree to rounding).
+ * No cudaMalloc, cudaFree, stream creation or allocating library call: the work runs on the calling thread's default
+ * stream (cudaStreamPerThread) and the call returns after it has drained.  Every call shares the one array, which keeps
+ * the previous call's contents (the entry point clears what must start at zero); calls that overlap on the GPU would race.
+ * Calls from several threads of one process are serialised by a lock inside the library. */
+#define MVBA_RPC_STATIC_MAX_N 65536
+#define MVBA_RPC_STATIC_MAX_PARTS 96
+int mvba_rpc_fit_static(int32_t device, int64_t n, const double* in_xy, const double* out_xy, int32_t rpc_degree,
+                        int32_t num_iterations, double parameter_tolerance, int32_t jacobian_mode, double* coeffs, double stats[4]);
+
 /* ---- measurement hooks (bench.py); device-resident inputs, CUDA-event timed ---- */
 /* Uploads parameters and keeps them resident. */
 int mvba_upload(mvba_problem* h);

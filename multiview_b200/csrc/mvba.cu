@@ -4,6 +4,7 @@
 #include <array>
 #include <chrono>
 #include <cstdlib>
+#include <mutex>
 
 #include "handle.cuh"
 #include "setup.cuh"
@@ -457,6 +458,51 @@ int mvba_rpc_fit(int32_t device, int64_t n, const double* in_xy, const double* o
   rc = F.init(n, in_xy, out_xy, p.multiProcessorCount); if (rc) return rc;
   std::vector<double> c; mvba::RpcFitStats st;
   rc = mvba::rpc_fit_all(F, rpc_degree, num_iterations, parameter_tolerance, jacobian_mode, c, &st); if (rc) return rc;
+  for (size_t i = 0; i < c.size(); i++) coeffs[i] = c[i];
+  if (stats) { stats[0] = st.initial_cost; stats[1] = st.final_cost; stats[2] = st.iterations; stats[3] = st.successful; }
+  return MVBA_OK;
+}
+
+}  // extern "C"
+
+// ---- mvba_rpc_fit_static: the same fit with every byte of device scratch in one file-scope array (no allocation) ----
+// Layout (doubles): [in 2n | out 2n | per-CTA partial normal equations | folded sums], RpcFitter::init_static.
+namespace {
+constexpr size_t kRpcStaticLen = 4 * (size_t)MVBA_RPC_STATIC_MAX_N + ((size_t)MVBA_RPC_STATIC_MAX_PARTS + 1) * (2 * (size_t)mvba::RPC_LD * mvba::RPC_LD + 2 * mvba::RPC_LD + 8);
+constexpr int kRpcStaticMaxDevices = 64;
+}  // namespace
+static __device__ __align__(256) double g_rpc_static_scratch[kRpcStaticLen];  // ~7.1 MB on every device that loads the library
+// In host code the name above is a host-side stand-in, not a device address: the address a kernel may use comes from
+// cudaGetSymbolAddress, asked once per device with that device current.
+static double* g_rpc_static_ptr[kRpcStaticMaxDevices];
+static int g_rpc_static_sms[kRpcStaticMaxDevices];
+static std::mutex g_rpc_static_mutex;
+
+extern "C" {
+
+int mvba_rpc_fit_static(int32_t device, int64_t n, const double* in_xy, const double* out_xy, int32_t rpc_degree, int32_t num_iterations,
+                        double parameter_tolerance, int32_t jacobian_mode, double* coeffs, double stats[4]) {
+  if (n < 1 || !in_xy || !out_xy || !coeffs || rpc_degree < 1 || rpc_degree > mvba::RPC_MAX_DEG || num_iterations < 0)
+    return fail(MVBA_EINVAL, "mvba_rpc_fit_static: bad argument");
+  if (n > MVBA_RPC_STATIC_MAX_N)
+    return fail(MVBA_EINVAL, "mvba_rpc_fit_static: " + std::to_string(n) + " samples exceed the static scratch area (MVBA_RPC_STATIC_MAX_N = " +
+                                 std::to_string(MVBA_RPC_STATIC_MAX_N) + "); use mvba_rpc_fit");
+  if (device < 0 || device >= kRpcStaticMaxDevices) return fail(MVBA_ENODEVICE, "mvba_rpc_fit_static: CUDA device ordinal out of range");
+  std::lock_guard<std::mutex> lock(g_rpc_static_mutex);  // one user of the array at a time within this process
+  if (!g_rpc_static_ptr[device]) {                        // set-up, once per device
+    int rc = ensure_device(device); if (rc) return rc;
+    MVBA_CUDA(cudaSetDevice(device));
+    double* ptr = nullptr;
+    MVBA_CUDA(cudaGetSymbolAddress((void**)&ptr, g_rpc_static_scratch));
+    int sms = 0; MVBA_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    g_rpc_static_sms[device] = sms; g_rpc_static_ptr[device] = ptr;
+  }
+  MVBA_CUDA(cudaSetDevice(device));
+  mvba::RpcFitter F;
+  int rc = F.init_static(n, in_xy, out_xy, g_rpc_static_sms[device], g_rpc_static_ptr[device], kRpcStaticLen, MVBA_RPC_STATIC_MAX_PARTS); if (rc) return rc;
+  std::vector<double> c; mvba::RpcFitStats st;
+  rc = mvba::rpc_fit_all(F, rpc_degree, num_iterations, parameter_tolerance, jacobian_mode, c, &st); if (rc) return rc;
+  MVBA_CUDA(cudaStreamSynchronize(F.stream));
   for (size_t i = 0; i < c.size(); i++) coeffs[i] = c[i];
   if (stats) { stats[0] = st.initial_cost; stats[1] = st.final_cost; stats[2] = st.iterations; stats[3] = st.successful; }
   return MVBA_OK;

@@ -166,7 +166,32 @@ struct RpcFitter {
     MVBA_CUDA(cudaFuncSetAttribute(rpc_accum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem()));
     return MVBA_OK;
   }
-  ~RpcFitter() { if (stream) cudaStreamDestroy(stream); }
+  // Caller-owned scratch instead of allocations (mvba_rpc_fit_static): `scratch` holds scratch_len doubles of DEVICE memory laid
+  // out as [in 2n | out 2n | per-CTA partial sums | folded sums]; nothing is allocated and nothing is freed, the stream is the
+  // calling thread's default stream.  The number of CTAs is capped by what the scratch holds.
+  bool borrowed = false;
+  static size_t static_len(int64_t n, int parts) { return 4 * (size_t)n + ((size_t)parts + 1) * rpc_part_len(0); }
+  int init_static(int64_t n, const double* in_xy, const double* out_xy, int sm_count, double* scratch, size_t scratch_len, int max_parts) {
+    N = n; borrowed = true; stream = cudaStreamPerThread;
+    grid = (int)std::max<int64_t>(1, std::min<int64_t>(std::min<int64_t>(2 * (int64_t)sm_count, max_parts), (n + RPC_CHUNK - 1) / RPC_CHUNK));
+    const size_t len = rpc_part_len(0);
+    if (static_len(n, grid) > scratch_len) return fail(MVBA_EINVAL, "rpc fit: the static scratch area is too small for this many samples");
+    d_in.p = scratch; d_in.n = 2 * (size_t)n;
+    d_out.p = d_in.p + d_in.n; d_out.n = 2 * (size_t)n;
+    d_part.p = d_out.p + d_out.n; d_part.n = len * grid;
+    d_sum.p = d_part.p + d_part.n; d_sum.n = len;
+    MVBA_CUDA(cudaMemcpyAsync(d_in.p, in_xy, 16 * (size_t)n, cudaMemcpyHostToDevice, stream));
+    MVBA_CUDA(cudaMemcpyAsync(d_out.p, out_xy, 16 * (size_t)n, cudaMemcpyHostToDevice, stream));
+    MVBA_CUDA(d_part.zero(stream));  // the area keeps the previous call's sums; tiles the kernel never writes must read as zero
+    MVBA_CUDA(d_sum.zero(stream));
+    h_sum.assign(len, 0.0);
+    MVBA_CUDA(cudaFuncSetAttribute(rpc_accum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem()));
+    return MVBA_OK;
+  }
+  ~RpcFitter() {
+    if (borrowed) { d_in.p = d_out.p = d_part.p = d_sum.p = nullptr; return; }  // not ours: the DBuf destructors must not free them
+    if (stream) cudaStreamDestroy(stream);
+  }
   static size_t smem() { return (2 * (size_t)RPC_CHUNK * RPC_LD + 2 * RPC_CHUNK) * sizeof(double); }
 
   // cost, J'J (two nh x nh blocks, full symmetric) and J'r at coefficients c (reference order)
