@@ -51,9 +51,34 @@ class ClockSampler:
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.index, self.rows, self.proc = index, [], None
+        self.index, self.rows, self.proc, self.nvml = index, [], None, None
+
+    def _poll_nvml(self):
+        """NVML in this process (what nvidia-smi reads, without a second process taking the driver's locks every poll: one
+        nvidia-smi poll inside a 70 ms timed region was seen to double the host-side wall time)."""
+        n, h = self.nvml
+        reasons = (("hw_slowdown", n.nvmlClocksThrottleReasonHwSlowdown), ("hw_thermal_slowdown", n.nvmlClocksThrottleReasonHwThermalSlowdown),
+                   ("sw_thermal_slowdown", n.nvmlClocksThrottleReasonSwThermalSlowdown), ("sw_power_cap", n.nvmlClocksThrottleReasonSwPowerCap))
+        mx = n.nvmlDeviceGetMaxClockInfo(h, n.NVML_CLOCK_SM)
+        while not self.done:
+            try:
+                sm = n.nvmlDeviceGetClockInfo(h, n.NVML_CLOCK_SM)
+                mask = n.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                self.rows.append([str(self.index), str(sm), str(mx), ""] + ["Active" if mask & bit else "Not Active" for _, bit in reasons])
+            except Exception:
+                pass
+            time.sleep(0.01)
 
     def start(self):
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nvml = (pynvml, pynvml.nvmlDeviceGetHandleByIndex(self.index))
+            self.done = False
+            threading.Thread(target=self._poll_nvml, daemon=True).start()
+            return
+        except Exception:
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
@@ -70,10 +95,14 @@ class ClockSampler:
         self.first = len(self.rows)
 
     def stop(self):
-        if self.proc is None:
+        if self.nvml is not None:
+            time.sleep(0.03)
+            self.done = True
+        elif self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.proc.terminate()
+        else:
+            time.sleep(0.15)
+            self.proc.terminate()
         sm, mx, reasons = [], [], set()
         for r in self.rows[max(0, getattr(self, "first", 0) - 1):]:
             try:
@@ -84,7 +113,7 @@ class ClockSampler:
                 if val.lower().startswith("active"):
                     reasons.add(name)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
-                "samples": len(sm)}
+                "samples": len(sm), "source": "nvml" if self.nvml is not None else "nvidia-smi"}
 
 
 def algorithmic_bytes(pr):
@@ -273,13 +302,18 @@ def run_ours(args):
     # over the measured launch time, against the measured FP64 peak of this GPU (tools/fp64_peak.cu -> profiles/r02_fp64_peak.json)
     fp64 = None
     try:
-        fb = json.load(open(os.path.join(ROOT, "profiles", "r02c_fp64_build.json")))
+        fb = json.load(open(os.path.join(ROOT, "profiles", "r02e_fp64_build.json")))
         pk = json.load(open(os.path.join(ROOT, "profiles", "r02_fp64_peak.json")))
         if fb.get("workload") == pr_full.name and world == 1 and args.scale == 1.0:
             peak_tf = max(pk["dfma_only"]["total_tflops"], pk["dmma_only"]["total_tflops"], pk["dfma_and_dmma"]["total_tflops"])
-            ach_tf = fb["fp64_flop_per_build"] / per_launch_s / 1e12
-            fp64 = {"achieved_tflops": ach_tf, "peak_tflops": peak_tf, "frac": ach_tf / peak_tf, "flop_per_launch": fb["fp64_flop_per_build"],
-                    "source": "profiles/r02c_fp64_build.json (ncu SASS counts) / profiles/r02_fp64_peak.json (measured DFMA+DMMA peak)"}
+            # the build after a rejected step keeps pass A's sums (same point, new damping): those launches run pass B only
+            flop_a = sum(v["flop"] for k, v in fb["kernels"].items() if "tile2" not in k)
+            reused = max(0, steps - s.num_successful_steps - (0 if log and log[-1]["step_accepted"] else 1))
+            flop_launch = fb["fp64_flop_per_build"] - flop_a * reused / max(s.num_build_launches, 1)
+            ach_tf = flop_launch / per_launch_s / 1e12
+            fp64 = {"achieved_tflops": ach_tf, "peak_tflops": peak_tf, "frac": ach_tf / peak_tf, "flop_per_launch": flop_launch,
+                    "launches_without_pass_a": reused,
+                    "source": "profiles/r02e_fp64_build.json (ncu SASS counts) / profiles/r02_fp64_peak.json (measured DFMA+DMMA peak)"}
     except Exception:
         pass
     plan = g.build_plan()

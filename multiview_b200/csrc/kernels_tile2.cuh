@@ -357,6 +357,7 @@ __global__ void __launch_bounds__(MVBA_T2_THREADS, 2) tile2_kernel(View v, Tile2
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
           const bool in = lane + d < seg_end;
+          if (!__any_sync(0xffffffffu, in)) break;  // no track of this warp is longer than d slots: the wider steps add nothing
 #pragma unroll
           for (int k = 0; k < 6; k++) { const double t = __shfl_down_sync(0xffffffffu, H[k], d); if (in) H[k] += t; }
 #pragma unroll

@@ -103,6 +103,9 @@ struct Solver {
   int maxposes = 1, maxitems = 1, maxdz = 1, vwmax = MVBA_VPOSE + 4;
   DBuf<int32_t> pairtab, row_ptr, col, slot, xcol, border_blk;
   DBuf<double> red;  // [Spp | Spb | Sbb | Fpp | Fbb | g | diagF | rhs | cost]  (one allreduce)
+  DBuf<double> redA; // same layout: what pass A (the camera part F'F, F'r) adds, kept so that the build after a REJECTED step -- same
+                     // point, new damping -- starts from it instead of evaluating pass A again (Ceres does not re-evaluate either)
+  bool redA_valid = false;
   size_t o_Spp = 0, o_Spb = 0, o_Sbb = 0, o_Fpp = 0, o_Fbb = 0, o_g = 0, o_diagF = 0, o_rhs = 0, o_cost = 0, o_gmaxe = 0, red_n = 0;
   DBuf<double> Dsq, Mpp, Mbb, work, jscale_f, jscale_e, Hinv, ge, diagE, lo, hi;
   DBuf<double> y, r, z, p, p2, q, ye, lm, pcg_scal;
@@ -141,7 +144,7 @@ struct Solver {
   size_t smem_tile2 = 0;
   // direct solver (linear_solver = 1): dense lower triangle + right-hand-side row, inverses of the diagonal blocks
   DBuf<double> cholA, cholLinv;
-  Reduced R{};
+  Reduced R{}, RA{};
   Bsr A{};
 };
 
@@ -263,6 +266,15 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
   R.Fpp = with_F ? rb + s->o_Fpp : nullptr; R.Fbb = with_F ? rb + s->o_Fbb : nullptr;
   R.g = rb + s->o_g; R.diagF = rb + s->o_diagF; R.rhs = rb + s->o_rhs;
   R.pairtab = s->pairtab.p; R.nb = nb; R.npc = s->npc; R.B = s->B; R.nf = s->nf;
+  MVBA_CUDA(s->redA.alloc(o)); s->redA_valid = false;
+  s->RA = R;
+  {
+    double* ra = s->redA.p;
+    Reduced& A2 = s->RA;
+    A2.Spp = ra + s->o_Spp; A2.Spb = ra + s->o_Spb; A2.Sbb = ra + s->o_Sbb;
+    A2.Fpp = with_F ? ra + s->o_Fpp : nullptr; A2.Fbb = with_F ? ra + s->o_Fbb : nullptr;
+    A2.g = ra + s->o_g; A2.diagF = ra + s->o_diagF; A2.rhs = ra + s->o_rhs;
+  }
   s->A.row_ptr = s->row_ptr.p; s->A.col = s->col.p; s->A.slot = s->slot.p; s->A.nb = nb;
   std::vector<int32_t> cam_items_host;
   {  // ---- pass A: residual blocks with f columns grouped by camera image (counting sort), chunked ----

@@ -20,10 +20,12 @@ struct Timers {
 };
 
 // mode 0: full fused build at x for the given radius; mode 1: squared column norms only.
-inline int run_build(mvba_problem* h, const mvba_solve_options& o, double radius, int mode, bool scaled, bool want_cost = true) {
+// reuse_A: the point has not moved since the previous mode-0 build (a rejected step): pass A's sums are taken from the copy kept then.
+inline int run_build(mvba_problem* h, const mvba_solve_options& o, double radius, int mode, bool scaled, bool want_cost = true, bool reuse_A = false) {
   Solver* s = h->solver;
   const View& v = h->view;
-  MVBA_CUDA(cudaMemsetAsync(s->red.p, 0, s->red_n * sizeof(double), h->stream));
+  reuse_A = reuse_A && s->redA_valid && mode == 0;
+  if (!reuse_A) MVBA_CUDA(cudaMemsetAsync(s->redA.p, 0, s->red_n * sizeof(double), h->stream));
   run_prep(h, h->d_x.p);
   BuildArgs a{};
   a.x = h->d_x.p; a.tab = h->d_tab.p; a.dtab = h->d_dtab.p;
@@ -33,7 +35,8 @@ inline int run_build(mvba_problem* h, const mvba_solve_options& o, double radius
   a.mode = mode; a.want_cost = want_cost ? 1 : 0; a.maxposes = s->maxposes; a.maxdz = s->maxdz; a.vwmax = s->vwmax;
   a.trk_list = nullptr; a.ntrk = v.P;
   if (s->tm) s->tm->begin(9);
-  if (s->nchunks > 0 && s->nf > 0 && s->cam_fast) {  // pass A, pose-type columns only: per-image 6 x 6 accumulators, then T'QT
+  if (reuse_A) {
+  } else if (s->nchunks > 0 && s->nf > 0 && s->cam_fast) {  // pass A, pose-type columns only: per-image 6 x 6 accumulators, then T'QT
     MVBA_CUDA(s->camQ.zero(h->stream));
     CamQArgs qa{};
     qa.x = h->d_x.p; qa.tab = h->d_tab.p; qa.dtab = h->d_dtab.p;
@@ -41,16 +44,18 @@ inline int run_build(mvba_problem* h, const mvba_solve_options& o, double radius
     camq_kernel<<<s->grid_camq, 256, 0, h->stream>>>(v, qa);
     CamFoldArgs fa{};
     fa.tab = h->d_tab.p; fa.coef = h->d_coef.p; fa.Q = s->camQ.p; fa.jscale_f = a.jscale_f; fa.mode = mode;
-    camfold_kernel<<<(v.C + 3) / 4, 128, 0, h->stream>>>(v, fa, s->R);
+    camfold_kernel<<<(v.C + 3) / 4, 128, 0, h->stream>>>(v, fa, s->RA);
     h->launches += 2;
   } else if (s->nchunks > 0 && s->nf > 0) {  // pass A: F'F, F'r, diag(F'F) by camera image
     CamPassArgs ca{};
     ca.x = h->d_x.p; ca.tab = h->d_tab.p; ca.dtab = h->d_dtab.p; ca.jscale_f = a.jscale_f;
     ca.chunk_cam = s->chunk_cam.p; ca.chunk_beg = s->chunk_beg.p; ca.citems = s->citems.p; ca.nchunks = s->nchunks;
     ca.batch_rows = s->cam_batch; ca.ldj = s->cam_ldj; ca.mode = mode; ca.coef = h->d_coef.p;
-    camera_pass_kernel<<<s->grid_cam, MVBA_CAM_THREADS, s->smem_cam, h->stream>>>(v, ca, s->R);
+    camera_pass_kernel<<<s->grid_cam, MVBA_CAM_THREADS, s->smem_cam, h->stream>>>(v, ca, s->RA);
     h->launches++;
   }
+  s->redA_valid = mode == 0;
+  MVBA_CUDA(cudaMemcpyAsync(s->red.p, s->redA.p, s->red_n * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));  // pass B adds to a copy
   if (v.P > 0 && mode == 1) {  // column norms: diag(E'E) per landmark
     colnorm_e_kernel<<<s->grid_backsub, 128, 0, h->stream>>>(v, h->d_x.p, h->d_tab.p, h->d_dtab.p, s->diagE.p);
     h->launches++;
@@ -221,7 +226,8 @@ inline int run_cost(mvba_problem* h, const double* x, double* out_slot) {
   const View& v = h->view;
   run_prep(h, x);
   int64_t total = v.N + v.n_dtri + v.n_dmesh + v.n_prior;
-  int grid = (int)std::max<int64_t>(1, std::min<int64_t>((total + 255) / 256, (int64_t)h->sm_count * 8));
+  static const int occ = [] { int o = 0; return cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, residual_kernel, 256, 0) == cudaSuccess && o > 0 ? o : 4; }();
+  int grid = (int)std::max<int64_t>(1, std::min<int64_t>((total + 255) / 256, (int64_t)h->sm_count * occ));  // one resident wave: a second, partial wave cost 20 %
   residual_kernel<<<grid, 256, 0, h->stream>>>(v, x, h->d_tab.p, h->d_dtab.p, 1, out_slot, nullptr);
   h->launches++;
   return MVBA_OK;
@@ -258,12 +264,12 @@ inline int solver_solve(mvba_problem* h, const mvba_solve_options& o, mvba_summa
     tm.end();
   }
   LmOpts lo{o.min_relative_decrease, o.parameter_tolerance, o.function_tolerance, o.max_trust_region_radius, o.min_trust_region_radius, o.gradient_tolerance};
-  bool have_cost = false;
+  bool have_cost = false, last_rejected = false;
   while (iter < o.max_num_iterations) {
     iter++;
     // ---- fused Jacobian + normal equations + Schur elimination at x ----
     tm.begin(PH_BUILD);
-    rc = run_build(h, o, radius, 0, scaled, !have_cost); if (rc) return rc;
+    rc = run_build(h, o, radius, 0, scaled, !have_cost, have_cost && last_rejected); if (rc) return rc;
     njac++;
     if (!have_cost) { MVBA_CUDA(cudaMemcpyAsync(s->lm.p + LM_COST, s->red.p + s->o_cost, sizeof(double), cudaMemcpyDeviceToDevice, h->stream)); }
     MVBA_CUDA(cudaMemsetAsync(s->lm.p + LM_GMAX, 0, sizeof(double), h->stream));
@@ -339,6 +345,7 @@ inline int solver_solve(mvba_problem* h, const mvba_solve_options& o, mvba_summa
       iter--; nlin -= cgit; term = MVBA_TERM_CONVERGENCE; break;
     }
     if (rec.step_accepted) nsucc++;
+    last_rejected = !rec.step_accepted;
     if (its && iter < max_its) its[iter] = rec;
     if (o.verbose) std::printf("%4d  %.6e   %9.2e    %.2e   %.2e  %9.2e  %.2e   %6d %s\n", iter, rec.cost, rec.cost_change, rec.gradient_max_norm,
                                rec.step_norm, rec.relative_decrease, rec.radius, cgit, rec.step_accepted ? "" : "(rejected)");
