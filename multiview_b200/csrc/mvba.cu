@@ -29,8 +29,10 @@ static int ensure_device(int device) {
 
 static int ready(mvba_problem* h) {
   if (!h) return fail(MVBA_EINVAL, "mvba: null handle");
-  int rc = ensure_device(h->device);
-  if (rc) return rc;
+  if (!h->stream) {  // the device is looked at once per handle: cudaGetDeviceProperties costs milliseconds, every call of the ABI comes through here
+    int rc = ensure_device(h->device);
+    if (rc) return rc;
+  }
   MVBA_CUDA(cudaSetDevice(h->device));
   if (!h->stream) {
     MVBA_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
@@ -260,7 +262,9 @@ int mvba_solve_options_init(mvba_solve_options* o) {
 }
 
 int mvba_solve(mvba_problem* h, const mvba_solve_options* o, mvba_summary* s, mvba_iteration* its, int32_t max_its) {
+  auto t_in = std::chrono::steady_clock::now();
   int rc = ready(h); if (rc) return rc;
+  if (std::getenv("MVBA_TIMING")) std::fprintf(stderr, "[mvba timing] ready %.3f ms\n", std::chrono::duration<double>(std::chrono::steady_clock::now() - t_in).count() * 1e3);
   if (!o || !s) return fail(MVBA_EINVAL, "mvba_solve: null argument");
   if (o->linear_solver != 0 && o->linear_solver != 1) return fail(MVBA_EINVAL, "mvba_solve: linear_solver must be 0 (PCG on the reduced camera system) or 1 (dense Cholesky)");
   if (o->preconditioner < 0 || o->preconditioner > 2) return fail(MVBA_EINVAL, "mvba_solve: preconditioner must be 0, 1 or 2");

@@ -240,7 +240,11 @@ inline int solver_solve(mvba_problem* h, const mvba_solve_options& o, mvba_summa
   int rc = solver_prepare(h, o.preconditioner == 0); if (rc) { solver_destroy(h); return rc; }
   Solver* s = h->solver;
   const View& v = h->view;
+  const bool timing = std::getenv("MVBA_TIMING") != nullptr;
+  auto lap = [&](const char* what) { if (timing) { cudaStreamSynchronize(h->stream); std::fprintf(stderr, "[mvba timing] %s at %.3f ms\n", what, std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() * 1e3); } };
+  lap("prepared");
   rc = upload_params(h); if (rc) return rc;
+  lap("uploaded");
   MVBA_CUDA(cudaMemsetAsync(h->d_err.p, 0, sizeof(int), h->stream));
   MVBA_CUDA(cudaMemsetAsync(s->lm.p, 0, LM_NSLOTS * sizeof(double), h->stream));
   const double init[2] = {o.initial_trust_region_radius, 2.0};
@@ -357,7 +361,9 @@ inline int solver_solve(mvba_problem* h, const mvba_solve_options& o, mvba_summa
   // an interpolation that left its bracket at ANY evaluated point (the reference aborts there, rig_calibrator.cc:346) is
   // reported before the write-back: the caller's arrays keep the values they came in with
   rc = check_device_error(h); if (rc) return rc;
+  lap("loop done");
   rc = download_params(h); if (rc) return rc;
+  lap("downloaded");
   float ms_all = 0;
   MVBA_CUDA(cudaEventElapsedTime(&ms_all, e_all0, e_all1));
   cudaEventDestroy(e_all0); cudaEventDestroy(e_all1);
