@@ -46,22 +46,21 @@ __device__ __forceinline__ void load_camtab(const CamTab* __restrict__ tab, int 
   }
 }
 
-template <bool WANT_J, bool WANT_E = true>
+// KEEP_R: R stays in registers across the projection (nine more live values) instead of being loaded a second time for E = A R:
+// for kernels that are bound by L1 requests (the back-substitution: five divergent 128-bit loads less per observation).
+template <bool WANT_J, bool WANT_E = true, bool KEEP_R = false>
 __device__ inline void eval_cam(const View& v, const double* __restrict__ x, const CamTab* __restrict__ tab, int64_t i,
                                 Item& it, double* Jd0, double* Jd1) {
   it.kind = MVBA_BLOCK_CAM; it.nr = 2;
   it.cid = v.cid[i]; it.pid = v.pid[i]; it.sensor = v.cam_sensor[it.cid];
   const double* X = x + v.x_xyz + 3 * (int64_t)it.pid;
   double Xw[3] = {X[0], X[1], X[2]};
-  {
-    double rt[12];
-    load_camtab(tab, it.cid, Xw, it.Xc, it.Z, rt);
-  }
+  double rt[12];
+  load_camtab(tab, it.cid, Xw, it.Xc, it.Z, rt);
   project_distort<WANT_J>(v.sens[it.sensor], x, it.Xc, v.pix[i], it.r, it.A, it.Jf, &it.Jc, Jd0, Jd1, v.fov_tab + 2 * it.sensor);
   it.r[2] = 0;
   if (WANT_J && WANT_E) {
-    double rt[10];  // R again (L1 hit) rather than 9 registers held across the projection
-    {
+    if (!KEEP_R) {  // R again (L1 hit) rather than 9 registers held across the projection
       const double2* q = reinterpret_cast<const double2*>(tab + it.cid);
 #pragma unroll
       for (int k = 0; k < 5; k++) { const double2 v2 = __ldg(q + k); rt[2 * k] = v2.x; rt[2 * k + 1] = v2.y; }

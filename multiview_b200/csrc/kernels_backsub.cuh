@@ -133,7 +133,7 @@ __device__ __forceinline__ void item_dir(const View& v, const BacksubArgs& a, co
 
 // DZ: some sensor's distortion coefficients float (their Jacobian columns are needed, dynamically indexed -> local memory);
 // without it the whole residual block stays in registers.
-template <bool DZ>
+template <bool DZ, bool KEEP_R = false>
 __global__ void __launch_bounds__(128, 4) backsub_kernel(View v, BacksubArgs a) {
   double mcc = 0;
   double jd[DZ ? 2 * MVBA_MAXDZ : 2];
@@ -148,7 +148,7 @@ __global__ void __launch_bounds__(128, 4) backsub_kernel(View v, BacksubArgs a) 
     for (int kind = 0; kind < 5; kind++) {
       for (int64_t j = r0[kind]; j < r1[kind]; j++) {
         Item it;
-        if (kind == 0) eval_cam<true>(v, a.x, a.tab, j, it, DZ ? jd : nullptr, DZ ? jd + MVBA_MAXDZ : nullptr);
+        if (kind == 0) eval_cam<true, true, KEEP_R>(v, a.x, a.tab, j, it, DZ ? jd : nullptr, DZ ? jd + MVBA_MAXDZ : nullptr);
         else if (kind == 1) eval_depth(v, a.x, a.tab, a.dtab, MVBA_BLOCK_DEPTH_TRI, j, it);
         else if (kind == 2) eval_depth(v, a.x, a.tab, a.dtab, MVBA_BLOCK_DEPTH_MESH, j, it);
         else eval_prior(v, a.x, j, it);

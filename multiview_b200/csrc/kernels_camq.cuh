@@ -107,6 +107,52 @@ __global__ void __launch_bounds__(256, 2) camq_kernel(View v, CamQArgs a) {
   }
 }
 
+// Cost of a candidate point over the same camera-major records: the lanes of a warp share the image, so its rotation and
+// translation are broadcast loads (the item-ordered residual_kernel gathers them per observation and is bound by L1 requests).
+// Covers every CAM and depth block; blocks without an image (landmark priors) stay with residual_kernel.
+__global__ void __launch_bounds__(256) camcost_kernel(View v, CamQArgs a, double* __restrict__ cost) {
+  const int tid = threadIdx.x;
+  double acc = 0;
+  for (int ch = blockIdx.x; ch < a.nchunks; ch += gridDim.x) {
+    const int cam = a.chunk_cam[ch];
+    const int i0 = a.chunk_beg[ch], i1 = a.chunk_beg[ch + 1];
+    double Rm[9], tv[3];
+    {
+      const CamTab& ct = a.tab[cam];
+#pragma unroll
+      for (int k = 0; k < 9; k++) Rm[k] = __ldg(ct.R + k);
+#pragma unroll
+      for (int k = 0; k < 3; k++) tv[k] = __ldg(ct.t + k);
+    }
+    const int sensor = v.cam_sensor[cam];
+    for (int i = i0 + tid; i < i1; i += 256) {
+      const int4 raw = __ldg(reinterpret_cast<const int4*>(a.crec) + i);
+      const int kind = ((uint32_t)raw.y >> 24) & 7;
+      double r[3], s;
+      double loss_a = v.robust_th;
+      if (kind == 0) {
+        const double* X = a.x + v.x_xyz + 3 * (int64_t)raw.x;
+        const double X0 = X[0], X1 = X[1], X2 = X[2];
+        double Xc[3];
+#pragma unroll
+        for (int k = 0; k < 3; k++) Xc[k] = Rm[3 * k] * X0 + Rm[3 * k + 1] * X1 + Rm[3 * k + 2] * X2 + tv[k];
+        double A[6], Jf[2], Jc;
+        project_distort<false>(v.sens[sensor], a.x, Xc, make_float2(__int_as_float(raw.z), __int_as_float(raw.w)), r, A, Jf, &Jc, nullptr, nullptr, v.fov_tab + 2 * sensor);
+        s = r[0] * r[0] + r[1] * r[1];
+      } else {
+        Item it;
+        eval_depth(v, a.x, a.tab, a.dtab, kind == 1 ? MVBA_BLOCK_DEPTH_TRI : MVBA_BLOCK_DEPTH_MESH, raw.x, it);
+        s = it.r[0] * it.r[0] + it.r[1] * it.r[1] + it.r[2] * it.r[2];
+        loss_a = it.loss_a;
+      }
+      double hr, sr;
+      cauchy(loss_a, s, &hr, &sr);
+      acc += hr;
+    }
+  }
+  block_accumulate(acc, cost);
+}
+
 struct CamFoldArgs {
   const CamTab* tab;
   const CamCoef* coef;

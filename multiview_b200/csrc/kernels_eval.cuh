@@ -68,10 +68,10 @@ __device__ __forceinline__ void block_accumulate(double val, double* out) {
 // Item index space: [0,N) CAM, then DEPTH_TRI, DEPTH_MESH, PRIOR.
 __global__ void __launch_bounds__(256) residual_kernel(View v, const double* __restrict__ x, const CamTab* __restrict__ tab,
                                                        const DepthTab* __restrict__ dtab, int apply_loss,
-                                                       double* __restrict__ cost, double* __restrict__ residuals) {
+                                                       double* __restrict__ cost, double* __restrict__ residuals, int64_t first = 0) {
   const int64_t total = v.N + v.n_dtri + v.n_dmesh + v.n_prior;
   double acc = 0;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+  for (int64_t i = first + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     Item it;
     int64_t row0;
     if (i < v.N) { eval_cam<false>(v, x, tab, i, it, nullptr, nullptr); row0 = v.obs_row0[i]; }

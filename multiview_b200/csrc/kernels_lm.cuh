@@ -74,12 +74,21 @@ __global__ void __launch_bounds__(256) update_kernel(int nx, int nf, const int32
     }
     xnew[i] = xn;
   }
-  // blocks are homogeneous enough: split the two parts by parameter kind
+  // the two parts by parameter kind; the four sums go through one block reduction
   const bool is_e = (i < nx) && xcol[i] >= nf;
-  block_accumulate(is_e ? 0.0 : s2, lm + LM_STEP2);
-  block_accumulate(is_e ? 0.0 : x2, lm + LM_XNORM2);
-  block_accumulate(is_e ? s2 : 0.0, lm + LM_STEP2E);
-  block_accumulate(is_e ? x2 : 0.0, lm + LM_XNORM2E);
+  double part[4] = {is_e ? 0.0 : s2, is_e ? 0.0 : x2, is_e ? s2 : 0.0, is_e ? x2 : 0.0};
+  __shared__ double sm4[4][8];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < 4; k++) { part[k] = warp_sum(part[k]); if (lane == 0) sm4[k][w] = part[k]; }
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    const int k = lane >> 3, j = lane & 7;  // 4 sums x 8 warps
+    double t = sm4[k][j];
+    t += __shfl_down_sync(0xffffffffu, t, 4, 8); t += __shfl_down_sync(0xffffffffu, t, 2, 8); t += __shfl_down_sync(0xffffffffu, t, 1, 8);
+    const int slot = k == 0 ? LM_STEP2 : k == 1 ? LM_XNORM2 : k == 2 ? LM_STEP2E : LM_XNORM2E;
+    if (j == 0 && t != 0.0) atomicAdd(lm + slot, t);
+  }
 }
 
 struct LmOpts { double min_rel_dec, param_tol, func_tol, max_radius, min_radius, grad_tol; };

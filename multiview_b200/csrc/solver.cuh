@@ -129,7 +129,7 @@ struct Solver {
   bool cam_fast = false;
   DBuf<double> camQ;
   DBuf<TSlot> crec;  // camera-major packed records (pass A without staged rows)
-  int grid_camq = 1;
+  int grid_camq = 1, grid_camcost = 1;
   // pass B fast path: tracks sorted by first pose block and cut into window tiles; the rest fall back
   // (static round tables: staged blocks, per-track slots, gather groups and their contributors, kernels_tile.cuh)
   DBuf<int32_t> tile_w0, tile_wn, tile_round0, round_trk0, round_blk0, round_grp0, fallback;
@@ -364,6 +364,9 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
       int occ_q = 1;
       MVBA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_q, camq_kernel, 256, 0));
       s->grid_camq = std::max(1, std::min(s->nchunks, h->sm_count * std::max(occ_q, 1)));
+      int occ_c = 1;
+      MVBA_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_c, camcost_kernel, 256, 0));
+      s->grid_camcost = std::max(1, std::min(s->nchunks, h->sm_count * std::max(occ_c, 1)));
     }
   }
   {  // ---- pass B fast path: window tiles ----

@@ -225,6 +225,21 @@ inline int run_dense(mvba_problem* h, int* iters_out) {
 inline int run_cost(mvba_problem* h, const double* x, double* out_slot) {
   const View& v = h->view;
   run_prep(h, x);
+  Solver* s = h->solver;
+  static const bool by_items = [] { const char* e = std::getenv("MVBA_COST_BY_ITEMS"); return e && e[0] == '1'; }();
+  if (s && s->cam_fast && s->nchunks > 0 && !by_items) {  // camera-major records: image data broadcast per warp, priors by the item kernel
+    CamQArgs qa{};
+    qa.x = x; qa.tab = h->d_tab.p; qa.dtab = h->d_dtab.p;
+    qa.chunk_cam = s->chunk_cam.p; qa.chunk_beg = s->chunk_beg.p; qa.citems = s->citems.p; qa.crec = s->crec.p; qa.nchunks = s->nchunks; qa.Q = nullptr;
+    camcost_kernel<<<s->grid_camcost, 256, 0, h->stream>>>(v, qa, out_slot);
+    h->launches++;
+    if (v.n_prior > 0) {
+      const int gp = (int)std::max<int64_t>(1, std::min<int64_t>((v.n_prior + 255) / 256, (int64_t)h->sm_count * 4));
+      residual_kernel<<<gp, 256, 0, h->stream>>>(v, x, h->d_tab.p, h->d_dtab.p, 1, out_slot, nullptr, v.N + v.n_dtri + v.n_dmesh);
+      h->launches++;
+    }
+    return MVBA_OK;
+  }
   int64_t total = v.N + v.n_dtri + v.n_dmesh + v.n_prior;
   static const int occ = [] { int o = 0; return cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, residual_kernel, 256, 0) == cudaSuccess && o > 0 ? o : 4; }();
   int grid = (int)std::max<int64_t>(1, std::min<int64_t>((total + 255) / 256, (int64_t)h->sm_count * occ));  // one resident wave: a second, partial wave cost 20 %
@@ -323,7 +338,7 @@ inline int solver_solve(mvba_problem* h, const mvba_solve_options& o, mvba_summa
       bool dz = false;
       for (int t = 0; t < v.T; t++) dz = dz || v.sens[t].c_dist >= 0;
       if (dz) backsub_kernel<true><<<s->grid_backsub, 128, 0, h->stream>>>(v, b);
-      else backsub_kernel<false><<<s->grid_backsub, 128, 0, h->stream>>>(v, b);
+      else backsub_kernel<false, true><<<s->grid_backsub, 128, 0, h->stream>>>(v, b);  // R kept in registers: the kernel is bound by L1 requests (measured: 0.02 ms per iteration)
       h->launches += 2;
     }
     update_kernel<<<(v.nx + tb - 1) / tb, tb, 0, h->stream>>>(v.nx, s->nf, s->xcol.p, h->d_x.p, s->y.p, s->ye.p, scaled ? s->jscale_f.p : nullptr,
