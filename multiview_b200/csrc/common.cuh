@@ -87,6 +87,7 @@ struct View {
   // observations (track-major, reference order)
   const int32_t *pid, *cid;
   const float2* pix;
+  const int4* orec;  // per observation {image, sensor, pixel x, pixel y (float bits)}: what cid / cam_sensor / pix hold, in one 128-bit load
   const int64_t* obs_row0;  // first residual row of the CAM block
   // depth-tri / depth-mesh blocks: index of the originating observation
   const int64_t *dtri_obs, *dmesh_obs, *dtri_row0, *dmesh_row0;

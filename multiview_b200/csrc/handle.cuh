@@ -84,6 +84,7 @@ struct mvba_problem {
   mvba::DBuf<int32_t> d_cam_sensor, d_cam_p0, d_cam_p1, d_pose_col, d_pid, d_cid, d_prior_pid;
   mvba::DBuf<double> d_cam_bs, d_cam_es, d_cam_cs, d_mesh, d_prior_ref, d_prior_w, d_prior_th;
   mvba::DBuf<float> d_pix, d_depth;
+  mvba::DBuf<int4> d_orec;
   mvba::DBuf<int64_t> d_obs_row0, d_dtri_obs, d_dtri_row0, d_dmesh_obs, d_dmesh_row0, d_prior_row0;
   mvba::DBuf<int64_t> d_trk_obs0, d_trk_dtri0, d_trk_dmesh0, d_trk_pm0, d_trk_pt0;
   mvba::DBuf<double> d_x, d_xnew;

@@ -49,15 +49,15 @@ __device__ __forceinline__ void load_camtab(const CamTab* __restrict__ tab, int 
 // KEEP_R: R stays in registers across the projection (nine more live values) instead of being loaded a second time for E = A R:
 // for kernels that are bound by L1 requests (the back-substitution: five divergent 128-bit loads less per observation).
 template <bool WANT_J, bool WANT_E = true, bool KEEP_R = false>
-__device__ inline void eval_cam(const View& v, const double* __restrict__ x, const CamTab* __restrict__ tab, int64_t i,
-                                Item& it, double* Jd0, double* Jd1) {
+__device__ inline void eval_cam_rec(const View& v, const double* __restrict__ x, const CamTab* __restrict__ tab, int cid, int pid, int sensor, float2 pix,
+                                    Item& it, double* Jd0, double* Jd1) {
   it.kind = MVBA_BLOCK_CAM; it.nr = 2;
-  it.cid = v.cid[i]; it.pid = v.pid[i]; it.sensor = v.cam_sensor[it.cid];
+  it.cid = cid; it.pid = pid; it.sensor = sensor;
   const double* X = x + v.x_xyz + 3 * (int64_t)it.pid;
   double Xw[3] = {X[0], X[1], X[2]};
   double rt[12];
   load_camtab(tab, it.cid, Xw, it.Xc, it.Z, rt);
-  project_distort<WANT_J>(v.sens[it.sensor], x, it.Xc, v.pix[i], it.r, it.A, it.Jf, &it.Jc, Jd0, Jd1, v.fov_tab + 2 * it.sensor);
+  project_distort<WANT_J>(v.sens[it.sensor], x, it.Xc, pix, it.r, it.A, it.Jf, &it.Jc, Jd0, Jd1, v.fov_tab + 2 * it.sensor);
   it.r[2] = 0;
   if (WANT_J && WANT_E) {
     if (!KEEP_R) {  // R again (L1 hit) rather than 9 registers held across the projection
@@ -72,6 +72,22 @@ __device__ inline void eval_cam(const View& v, const double* __restrict__ x, con
         it.E[3 * a + b] = it.A[3 * a] * rt[b] + it.A[3 * a + 1] * rt[3 + b] + it.A[3 * a + 2] * rt[6 + b];
   }
   it.loss_a = v.robust_th; it.weight = 1.0;
+}
+
+template <bool WANT_J, bool WANT_E = true, bool KEEP_R = false>
+__device__ inline void eval_cam(const View& v, const double* __restrict__ x, const CamTab* __restrict__ tab, int64_t i,
+                                Item& it, double* Jd0, double* Jd1) {
+  const int cid = v.cid[i];
+  eval_cam_rec<WANT_J, WANT_E, KEEP_R>(v, x, tab, cid, v.pid[i], v.cam_sensor[cid], v.pix[i], it, Jd0, Jd1);
+}
+
+// The same block from the packed observation record (image, sensor, pixel in one 128-bit load) and a landmark the caller knows:
+// for thread-per-track kernels, whose per-observation loads are all divergent.
+template <bool WANT_J, bool WANT_E = true, bool KEEP_R = false>
+__device__ inline void eval_cam_packed(const View& v, const double* __restrict__ x, const CamTab* __restrict__ tab, int64_t i, int pid,
+                                       Item& it, double* Jd0, double* Jd1) {
+  const int4 rc = __ldg(v.orec + i);
+  eval_cam_rec<WANT_J, WANT_E, KEEP_R>(v, x, tab, rc.x, pid, rc.y, make_float2(__int_as_float(rc.z), __int_as_float(rc.w)), it, Jd0, Jd1);
 }
 
 // kind = DEPTH_TRI or DEPTH_MESH; j = index inside that kind.

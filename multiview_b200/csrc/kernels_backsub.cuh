@@ -148,7 +148,7 @@ __global__ void __launch_bounds__(128, 4) backsub_kernel(View v, BacksubArgs a) 
     for (int kind = 0; kind < 5; kind++) {
       for (int64_t j = r0[kind]; j < r1[kind]; j++) {
         Item it;
-        if (kind == 0) eval_cam<true, true, KEEP_R>(v, a.x, a.tab, j, it, DZ ? jd : nullptr, DZ ? jd + MVBA_MAXDZ : nullptr);
+        if (kind == 0) eval_cam_packed<true, true, KEEP_R>(v, a.x, a.tab, j, p, it, DZ ? jd : nullptr, DZ ? jd + MVBA_MAXDZ : nullptr);
         else if (kind == 1) eval_depth(v, a.x, a.tab, a.dtab, MVBA_BLOCK_DEPTH_TRI, j, it);
         else if (kind == 2) eval_depth(v, a.x, a.tab, a.dtab, MVBA_BLOCK_DEPTH_MESH, j, it);
         else eval_prior(v, a.x, j, it);
@@ -194,7 +194,7 @@ __global__ void __launch_bounds__(128, 4) colnorm_e_kernel(View v, const double*
     for (int kind = 0; kind < 5; kind++) {
       for (int64_t j = r0[kind]; j < r1[kind]; j++) {
         Item it;
-        if (kind == 0) eval_cam<true>(v, x, tab, j, it, nullptr, nullptr);
+        if (kind == 0) eval_cam_packed<true>(v, x, tab, j, p, it, nullptr, nullptr);
         else if (kind == 1) eval_depth(v, x, tab, dtab, MVBA_BLOCK_DEPTH_TRI, j, it);
         else if (kind == 2) eval_depth(v, x, tab, dtab, MVBA_BLOCK_DEPTH_MESH, j, it);
         else eval_prior(v, x, j, it);

@@ -212,6 +212,15 @@ inline int setup(mvba_problem* h) {
   MVBA_CUDA(h->d_cam_bs.upload(h->h_cam_bs)); MVBA_CUDA(h->d_cam_es.upload(h->h_cam_es)); MVBA_CUDA(h->d_cam_cs.upload(h->cam_stamp));
   MVBA_CUDA(h->d_pose_col.upload(h->h_pose_col));
   MVBA_CUDA(h->d_pid.upload(h->opid)); MVBA_CUDA(h->d_cid.upload(h->ocid)); MVBA_CUDA(h->d_pix.upload(h->opix));
+  {
+    std::vector<int4> orec(h->ocid.size());
+    for (size_t i = 0; i < orec.size(); i++) {
+      int4 r; r.x = h->ocid[i]; r.y = h->cam_sensor[r.x];
+      std::memcpy(&r.z, &h->opix[2 * i], 4); std::memcpy(&r.w, &h->opix[2 * i + 1], 4);
+      orec[i] = r;
+    }
+    MVBA_CUDA(h->d_orec.upload(orec));
+  }
   MVBA_CUDA(h->d_obs_row0.upload(h->h_obs_row0));
   MVBA_CUDA(h->d_dtri_obs.upload(h->h_dtri_obs)); MVBA_CUDA(h->d_dtri_row0.upload(h->h_dtri_row0));
   MVBA_CUDA(h->d_dmesh_obs.upload(h->h_dmesh_obs)); MVBA_CUDA(h->d_dmesh_row0.upload(h->h_dmesh_row0));
@@ -227,7 +236,7 @@ inline int setup(mvba_problem* h) {
   MVBA_CUDA(h->d_scalars.alloc(64)); MVBA_CUDA(h->d_err.alloc(1));
   v.cam_sensor = h->d_cam_sensor.p; v.cam_p0 = h->d_cam_p0.p; v.cam_p1 = h->d_cam_p1.p;
   v.cam_bs = h->d_cam_bs.p; v.cam_es = h->d_cam_es.p; v.cam_cs = h->d_cam_cs.p; v.pose_col = h->d_pose_col.p;
-  v.pid = h->d_pid.p; v.cid = h->d_cid.p; v.pix = reinterpret_cast<const float2*>(h->d_pix.p); v.obs_row0 = h->d_obs_row0.p;
+  v.pid = h->d_pid.p; v.cid = h->d_cid.p; v.pix = reinterpret_cast<const float2*>(h->d_pix.p); v.orec = h->d_orec.p; v.obs_row0 = h->d_obs_row0.p;
   v.dtri_obs = h->d_dtri_obs.p; v.dmesh_obs = h->d_dmesh_obs.p; v.dtri_row0 = h->d_dtri_row0.p; v.dmesh_row0 = h->d_dmesh_row0.p;
   v.depth_xyz = h->d_depth.p; v.mesh_xyz = h->d_mesh.p;
   v.prior_pid = h->d_prior_pid.p; v.prior_ref = h->d_prior_ref.p; v.prior_w = h->d_prior_w.p; v.prior_th = h->d_prior_th.p; v.prior_row0 = h->d_prior_row0.p;

@@ -21,12 +21,15 @@ struct Timers {
 
 // mode 0: full fused build at x for the given radius; mode 1: squared column norms only.
 // reuse_A: the point has not moved since the previous mode-0 build (a rejected step): pass A's sums are taken from the copy kept then.
-inline int run_build(mvba_problem* h, const mvba_solve_options& o, double radius, int mode, bool scaled, bool want_cost = true, bool reuse_A = false) {
+// tables_current: the per-image tables on the device already belong to this point (the candidate of the previous iteration was
+// accepted: its cost evaluation prepared them).
+inline int run_build(mvba_problem* h, const mvba_solve_options& o, double radius, int mode, bool scaled, bool want_cost = true, bool reuse_A = false,
+                     bool tables_current = false) {
   Solver* s = h->solver;
   const View& v = h->view;
   reuse_A = reuse_A && s->redA_valid && mode == 0;
   if (!reuse_A) MVBA_CUDA(cudaMemsetAsync(s->redA.p, 0, s->red_n * sizeof(double), h->stream));
-  run_prep(h, h->d_x.p);
+  if (!tables_current) run_prep(h, h->d_x.p);
   BuildArgs a{};
   a.x = h->d_x.p; a.tab = h->d_tab.p; a.dtab = h->d_dtab.p;
   a.jscale_f = scaled ? s->jscale_f.p : nullptr; a.jscale_e = scaled ? s->jscale_e.p : nullptr;
@@ -283,12 +286,12 @@ inline int solver_solve(mvba_problem* h, const mvba_solve_options& o, mvba_summa
     tm.end();
   }
   LmOpts lo{o.min_relative_decrease, o.parameter_tolerance, o.function_tolerance, o.max_trust_region_radius, o.min_trust_region_radius, o.gradient_tolerance};
-  bool have_cost = false, last_rejected = false;
+  bool have_cost = false, last_rejected = false, last_accepted = false;
   while (iter < o.max_num_iterations) {
     iter++;
     // ---- fused Jacobian + normal equations + Schur elimination at x ----
     tm.begin(PH_BUILD);
-    rc = run_build(h, o, radius, 0, scaled, !have_cost, have_cost && last_rejected); if (rc) return rc;
+    rc = run_build(h, o, radius, 0, scaled, !have_cost, have_cost && last_rejected, last_accepted); if (rc) return rc;
     njac++;
     if (!have_cost) { MVBA_CUDA(cudaMemcpyAsync(s->lm.p + LM_COST, s->red.p + s->o_cost, sizeof(double), cudaMemcpyDeviceToDevice, h->stream)); }
     MVBA_CUDA(cudaMemsetAsync(s->lm.p + LM_GMAX, 0, sizeof(double), h->stream));
@@ -364,7 +367,7 @@ inline int solver_solve(mvba_problem* h, const mvba_solve_options& o, mvba_summa
       iter--; nlin -= cgit; term = MVBA_TERM_CONVERGENCE; break;
     }
     if (rec.step_accepted) nsucc++;
-    last_rejected = !rec.step_accepted;
+    last_rejected = !rec.step_accepted; last_accepted = rec.step_accepted != 0;
     if (its && iter < max_its) its[iter] = rec;
     if (o.verbose) std::printf("%4d  %.6e   %9.2e    %.2e   %.2e  %9.2e  %.2e   %6d %s\n", iter, rec.cost, rec.cost_change, rec.gradient_max_norm,
                                rec.step_norm, rec.relative_decrease, rec.radius, cgit, rec.step_accepted ? "" : "(rejected)");
