@@ -302,7 +302,7 @@ def run_ours(args):
     # over the measured launch time, against the measured FP64 peak of this GPU (tools/fp64_peak.cu -> profiles/r02_fp64_peak.json)
     fp64 = None
     try:
-        fb = json.load(open(os.path.join(ROOT, "profiles", "r02e_fp64_build.json")))
+        fb = json.load(open(os.path.join(ROOT, "profiles", "r02f_fp64_build.json")))
         pk = json.load(open(os.path.join(ROOT, "profiles", "r02_fp64_peak.json")))
         if fb.get("workload") == pr_full.name and world == 1 and args.scale == 1.0:
             peak_tf = max(pk["dfma_only"]["total_tflops"], pk["dmma_only"]["total_tflops"], pk["dfma_and_dmma"]["total_tflops"])
@@ -313,7 +313,7 @@ def run_ours(args):
             ach_tf = flop_launch / per_launch_s / 1e12
             fp64 = {"achieved_tflops": ach_tf, "peak_tflops": peak_tf, "frac": ach_tf / peak_tf, "flop_per_launch": flop_launch,
                     "launches_without_pass_a": reused,
-                    "source": "profiles/r02e_fp64_build.json (ncu SASS counts) / profiles/r02_fp64_peak.json (measured DFMA+DMMA peak)"}
+                    "source": "profiles/r02f_fp64_build.json (ncu SASS counts) / profiles/r02_fp64_peak.json (measured DFMA+DMMA peak)"}
     except Exception:
         pass
     plan = g.build_plan()
