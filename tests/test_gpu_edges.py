@@ -125,3 +125,16 @@ def test_wide_windows_use_the_larger_accumulator_instantiations(obs_per_track, i
     a, b, plan = _both(pr, oracle_lib, product_lib, 4)
     assert plan["pass_b"] == want[0] and plan["blocks_per_warp"] >= want[1] and plan["fallback_tracks"] == 0, plan
     _same_path(a, b, pr)
+
+
+def test_depth_mesh_and_prior_blocks_on_the_fast_kernels(oracle_lib, product_lib):
+    """Depth, depth-mesh, mesh and triangulation-prior blocks with every intrinsic and depth transform FIXED: the pass then takes
+    the per-image accumulators of pass A, the staged tile kernel and the camera-major candidate cost (camcost_kernel evaluates the
+    depth kinds itself, landmark priors go to residual_kernel with an offset) -- the kernels BASELINE config 5 runs, which itself
+    has no such blocks."""
+    pr = synth.make_problem(seed=23, sensors="rig3", num_ref=12, num_landmarks=500, obs_per_track=5, depth=True, mesh=True,
+                            depth_tri_weight=1000.0, depth_mesh_weight=50.0, mesh_tri_weight=25.0, tri_weight=0.5)
+    a, b, plan = _both(pr, oracle_lib, product_lib, 6)
+    assert plan["pass_a_accumulators"] == 1 and plan["pass_b"] == 2, plan
+    assert b[0].num_successful_steps >= 3
+    _same_path(a, b, pr)
