@@ -64,8 +64,13 @@ struct Tile2Args {
 
 // Shared memory: Gs[L8max][KK] | pack[ccap] | blob | Xs[2][K][6] | Ls[K][6] | cs[L8max] | rec[icap + icap / 8 + 1] | rcid[same] | mbarriers
 // (the bulk-copy destinations first: they need 16-byte alignment)
+// Row length of Gs: 3 K rounded up to 8 (mod 16) doubles.  The tensor-core phase reads every fragment as ONE 128-bit load that
+// serves two DMMAs (columns k0 + 2 tig and k0 + 2 tig + 1: the product Gs Gs' does not care in which order the columns are
+// contracted, as long as both operands use the same one); a quarter warp (2 rows x 4 x 16 bytes) then covers all banks once.
+__host__ __device__ inline int tile2_kk(int K) { int kk = 3 * K; while ((kk & 15) != 8) kk++; return kk; }
+
 __host__ __device__ inline size_t tile2_smem(int K, int icap, int ccap, int L8max, int blob_cap) {
-  const size_t KK = tile_kk(K);
+  const size_t KK = tile2_kk(K);
   size_t n = (size_t)L8max * KK * 8 + (size_t)ccap * sizeof(CamPack) + (size_t)blob_cap;
   n += ((size_t)2 * K * 6 + (size_t)K * 6 + (size_t)L8max) * 8;
   n += (size_t)t2_rcap(icap) * sizeof(TRec2);
@@ -174,7 +179,7 @@ __global__ void __launch_bounds__(MVBA_T2_THREADS, 2) tile2_kernel(View v, Tile2
   extern __shared__ __align__(16) unsigned char smem_raw[];
   constexpr int NT = MVBA_T2_THREADS, NW = NT / 32;
   const int tid = threadIdx.x, lane = tid & 31, wib = tid >> 5;
-  const int K = a.K, KK = tile_kk(K);
+  const int K = a.K, KK = tile2_kk(K);
   double* Gs = reinterpret_cast<double*>(smem_raw);
   CamPack* pack_s = reinterpret_cast<CamPack*>(Gs + (size_t)a.L8max * KK);
   unsigned char* blob_s = reinterpret_cast<unsigned char*>(pack_s + a.ccap);
@@ -432,19 +437,24 @@ __global__ void __launch_bounds__(MVBA_T2_THREADS, 2) tile2_kernel(View v, Tile2
       //      are fixed for the tile: the inner loop is two shared loads and one DMMA per block, nothing else (slots past
       //      the warp's last block repeat block 0 into accumulators that are never flushed) ----
       {
-        const int kend = (3 * kc + 3) & ~3;
-        const double* base = Gs + (size_t)gid * KK + tig;
+        const int kend = (3 * kc + 7) & ~7;  // columns past 3 kc are zero (cleared with the rest of Gs)
+        const double* base = Gs + (size_t)gid * KK + 2 * tig;
 #pragma unroll 2
-        for (int k0 = 0; k0 < kend; k0 += 4) {
+        for (int k0 = 0; k0 < kend; k0 += 8) {
           const double* kb = base + k0;
-          double av = kb[offa[0]];
+          double2 av = *reinterpret_cast<const double2*>(kb + offa[0]);
+          double by[MAXS], ay[MAXS];
 #pragma unroll
           for (int sl = 0; sl < MAXS; sl++) {
             // (slots past the warp's last block repeat block 0 into accumulators that are never flushed: a warp-uniform guard
             //  around the DMMA was measured 10 % slower than the idle DMMAs it saves)
-            if (sl > 0 && ((newrow >> sl) & 1)) av = kb[offa[sl]];  // the A fragment stays while the warp's blocks stay in one block row
-            dmma884(acc[sl][0], acc[sl][1], av, kb[offb[sl]]);
+            if (sl > 0 && ((newrow >> sl) & 1)) av = *reinterpret_cast<const double2*>(kb + offa[sl]);  // the A fragment stays while the warp's blocks stay in one block row
+            const double2 bv = *reinterpret_cast<const double2*>(kb + offb[sl]);
+            dmma884(acc[sl][0], acc[sl][1], av.x, bv.x);
+            ay[sl] = av.y; by[sl] = bv.y;
           }
+#pragma unroll
+          for (int sl = 0; sl < MAXS; sl++) dmma884(acc[sl][0], acc[sl][1], ay[sl], by[sl]);
         }
       }
       T2PROF(6);
