@@ -111,3 +111,35 @@ def test_config4_full_size_properties(product_lib):
     assert np.array_equal(pr.distortion[half:], dist0[half:])
     assert not np.array_equal(pr.distortion[:half], dist0[:half])
     g.close()
+
+
+def test_config5_full_size_properties(product_lib):
+    """Config 5 at FULL size (2000 frames x 1 M landmarks x 8 observations, the bench workload; the oracle needs minutes per
+    iteration there): properties that need no oracle.  (i) the cost the fused build reports at the start equals the stand-alone
+    residual pass (item order, residual_kernel); (ii) the cost sequence is non-increasing, accepted steps have a positive relative
+    decrease, rejected ones leave the cost alone -- this run has both, so the build that keeps pass A's sums after a rejected step
+    is exercised; (iii) the cost of the last accepted candidate -- computed over the camera-major records (camcost_kernel) inside
+    the solve -- equals the stand-alone residual pass at the returned parameters; (iv) a second solve from the same start
+    reproduces the trajectory (the sums are atomic, so to rounding, not to the bit)."""
+    pr = synth.config(5, scale=1.0)
+    snap = pr.snapshot()
+    g = _abi.Binding(product_lib, "mvba_", pr)
+    c0, _ = g.evaluate(True, want_residuals=False)
+    s, log = g.solve(_abi.default_options(max_num_iterations=12))
+    plan = g.build_plan()
+    assert plan["pass_a_accumulators"] == 1 and plan["pass_b"] == 2 and plan["fallback_tracks"] == 0, plan
+    assert abs(s.initial_cost - c0) <= 1e-10 * c0
+    costs = [l["cost"] for l in log]
+    assert all(b <= a * (1 + 1e-15) for a, b in zip(costs, costs[1:]))
+    accepted = [l["step_accepted"] for l in log[1:]]
+    assert any(accepted) and not all(accepted), accepted
+    assert all(l["relative_decrease"] > 0 for l in log[1:] if l["step_accepted"])
+    assert all(b == a for a, b, l in zip(costs, costs[1:], log[1:]) if not l["step_accepted"])
+    assert s.final_cost < 0.2 * s.initial_cost
+    c1, _ = g.evaluate(True, want_residuals=False)
+    assert abs(c1 - s.final_cost) <= 1e-10 * c1
+    pr.restore(snap)
+    s2, log2 = g.solve(_abi.default_options(max_num_iterations=12))
+    assert [l["step_accepted"] for l in log2] == [l["step_accepted"] for l in log]
+    assert max(abs(a["cost"] - b["cost"]) / b["cost"] for a, b in zip(log2, log)) <= 1e-9
+    g.close()
