@@ -37,11 +37,13 @@ __global__ void jscale_kernel(int64_t n, const double* __restrict__ n2, double* 
 __global__ void gradmax_kernel(int nf, int64_t ne, const double* __restrict__ g, const double* __restrict__ ge,
                                const double* __restrict__ sf, const double* __restrict__ se, const double* __restrict__ extra, int nextra,
                                double* __restrict__ out) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   double v = 0;
-  if (i < nf) v = fabs(g[i] / (sf ? sf[i] : 1.0));
-  else if (i < nf + ne) { int64_t k = i - nf; v = fabs(ge[k] / (se ? se[k] : 1.0)); }
-  else if (i < nf + ne + nextra) v = extra[i - nf - ne];
+  // grid-stride (the launch bounds the grid): the atomics of all CTAs land on ONE address, and thousands of them serialise
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nf + ne + nextra; i += (int64_t)gridDim.x * blockDim.x) {
+    if (i < nf) v = fmax(v, fabs(g[i] / (sf ? sf[i] : 1.0)));
+    else if (i < nf + ne) { int64_t k = i - nf; v = fmax(v, fabs(ge[k] / (se ? se[k] : 1.0))); }
+    else v = fmax(v, extra[i - nf - ne]);
+  }
   for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
   __shared__ double wmax[32];  // one atomic per CTA: a per-warp atomic on ONE address serialises ~100 k updates at 3 M landmarks
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -60,23 +62,20 @@ __global__ void __launch_bounds__(256) update_kernel(int nx, int nf, const int32
                                                       const double* __restrict__ sf, const double* __restrict__ se,
                                                       const double* __restrict__ lo, const double* __restrict__ hi,
                                                       double* __restrict__ xnew, double* __restrict__ lm) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  double s2 = 0, x2 = 0;
-  if (i < nx) {
-    int c = xcol[i];
+  // grid-stride (the launch bounds the grid: every CTA ends in four atomics on the same four addresses); the two parts by parameter kind
+  double part[4] = {0.0, 0.0, 0.0, 0.0};
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nx; i += gridDim.x * blockDim.x) {
+    const int c = xcol[i];
     double xi = x[i], xn = xi;
     if (c >= 0) {
       double d = (c < nf) ? -yf[c] * (sf ? sf[c] : 1.0) : -ye[c - nf] * (se ? se[c - nf] : 1.0);
       xn = xi + d;
       if (lo) xn = fmin(fmax(xn, lo[i]), hi[i]);
       d = xn - xi;
-      s2 = d * d; x2 = xi * xi;
+      if (c >= nf) { part[2] += d * d; part[3] += xi * xi; } else { part[0] += d * d; part[1] += xi * xi; }
     }
     xnew[i] = xn;
   }
-  // the two parts by parameter kind; the four sums go through one block reduction
-  const bool is_e = (i < nx) && xcol[i] >= nf;
-  double part[4] = {is_e ? 0.0 : s2, is_e ? 0.0 : x2, is_e ? s2 : 0.0, is_e ? x2 : 0.0};
   __shared__ double sm4[4][8];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
 #pragma unroll

@@ -349,7 +349,7 @@ __device__ __forceinline__ double spmv_row_dot(const Reduced& S, const Bsr& A, c
 template <bool DOT>
 __device__ __forceinline__ double spmv_row_sm(const Reduced& S, const Bsr& A, const double* sm_pp, const double* sm_pb, int e0, int r0,
                                               const double* x, double* y, int w, int lane,
-                                              const double* z = nullptr, double beta = 0.0, double* pn = nullptr) {
+                                              const double* z = nullptr, double beta = 0.0, double* pn = nullptr, double* qb_s = nullptr) {
   const int B = S.B;
   double dot = 0;
   double acc[7] = {0, 0, 0, 0, 0, 0, 0};
@@ -372,7 +372,9 @@ __device__ __forceinline__ double spmv_row_sm(const Reduced& S, const Bsr& A, co
     double t = 0;
 #pragma unroll
     for (int r = 0; r < 7; r++) { const double s = sm_pb[(size_t)(7 * (w - r0) + r) * B + b]; acc[r] += s * xb; t += s * xr[r]; }
-    atomicAdd(y + S.npc + b, t);
+    // the border rows of y collect a term from EVERY pose row: summed per CTA in shared memory first (qb_s), one global atomic per
+    // CTA and border row afterwards -- 2000 atomics on the same 14 addresses per product were 6 us of every CG iteration
+    if (qb_s) atomicAdd(qb_s + b, t); else atomicAdd(y + S.npc + b, t);
     if (DOT) dot += xb * t;
   }
 #pragma unroll
@@ -383,6 +385,8 @@ __device__ __forceinline__ double spmv_row_sm(const Reduced& S, const Bsr& A, co
   }
   return dot;
 }
+
+#define MVBA_PCG_QB 192  // border columns whose per-CTA sums fit the shared array (more: global atomics per row, as before)
 
 __global__ void __launch_bounds__(512) pcg_fused_kernel(Reduced S, Bsr A, const double* Mpp, const double* Mbb, const double* b, double* x,
                                                          double* r, double* z, double* p, double* q, PcgScal sc, double eta, int min_it,
@@ -410,6 +414,10 @@ __global__ void __launch_bounds__(512) pcg_fused_kernel(Reduced S, Bsr A, const 
     double* pb = pcg_sm + (size_t)(e1 - e0) * 49;
     for (int i = threadIdx.x; i < 7 * (r1 - r0) * B; i += blockDim.x) pb[i] = S.Spb[(size_t)7 * r0 * B + i];
   }
+  // per-CTA sums of the border rows of a product (spmv_row_sm), flushed with one atomic per CTA and row
+  __shared__ double qb_sm[MVBA_PCG_QB];
+  double* qb_s = (rows_per_cta > 0 && B <= MVBA_PCG_QB) ? qb_sm : nullptr;
+  if (qb_s) for (int i = threadIdx.x; i < B; i += blockDim.x) qb_s[i] = 0.0;
   // two direction buffers: po holds the current p, pn receives the next one inside the product (no separate update pass)
   double* po = p; double* pn = p2;
   for (int i = gtid; i < nf; i += nthr) { x[i] = 0; r[i] = b[i]; po[i] = 0; pn[i] = 0; if (i >= npc) q[i] = 0; }
@@ -480,12 +488,13 @@ __global__ void __launch_bounds__(512) pcg_fused_kernel(Reduced S, Bsr A, const 
     {
       double v = 0;
       if (rows_per_cta > 0) {
-        for (int w = r0 + wib; w < r1; w += nwib) v += spmv_row_sm<true>(S, A, sm_pp, sm_pb, e0, r0, po, q, w, lane, z, beta, pn);
+        for (int w = r0 + wib; w < r1; w += nwib) v += spmv_row_sm<true>(S, A, sm_pp, sm_pb, e0, r0, po, q, w, lane, z, beta, pn, qb_s);
         if (blockIdx.x == gridDim.x - 1) for (int w = nb + wib; w < nb + B; w += nwib) v += spmv_row_dot(S, A, po, q, w, lane, z, beta, pn);
       } else {
         for (int w = gwarp; w < nb + B; w += nwarp) v += spmv_row_dot(S, A, po, q, w, lane, z, beta, pn);
       }
-      block_accumulate(v, sc.it + 4 * it + 1);
+      block_accumulate(v, sc.it + 4 * it + 1);  // (its barriers also order the shared-memory sums below)
+      if (qb_s) for (int i = threadIdx.x; i < B; i += blockDim.x) { const double t = qb_s[i]; qb_s[i] = 0.0; if (t != 0.0) atomicAdd(q + npc + i, t); }
     }
     grid.sync();
     { double* t = po; po = pn; pn = t; }
@@ -497,7 +506,11 @@ __global__ void __launch_bounds__(512) pcg_fused_kernel(Reduced S, Bsr A, const 
       for (int i = gtid; i < nf; i += nthr) { x[i] += alpha * po[i]; if (i >= npc) q[i] = 0; }
       grid.sync();
       if (rows_per_cta > 0) {
-        for (int w = r0 + wib; w < r1; w += nwib) spmv_row_sm<false>(S, A, sm_pp, sm_pb, e0, r0, x, q, w, lane);
+        for (int w = r0 + wib; w < r1; w += nwib) spmv_row_sm<false>(S, A, sm_pp, sm_pb, e0, r0, x, q, w, lane, nullptr, 0.0, nullptr, qb_s);
+        if (qb_s) {
+          __syncthreads();
+          for (int i = threadIdx.x; i < B; i += blockDim.x) { const double t = qb_s[i]; qb_s[i] = 0.0; if (t != 0.0) atomicAdd(q + npc + i, t); }
+        }
         if (blockIdx.x == gridDim.x - 1) for (int w = nb + wib; w < nb + B; w += nwib) spmv_row(S, A, x, q, w, lane);
       } else {
         for (int w = gwarp; w < nb + B; w += nwarp) spmv_row(S, A, x, q, w, lane);

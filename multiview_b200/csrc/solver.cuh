@@ -119,7 +119,7 @@ struct Solver {
   int pcg_coop_grid = 0;  // > 0: CTAs of the single-launch PCG (cooperative); 0: step kernels
   int pcg_rows_per_cta = 0;  // > 0: every CTA keeps the blocks of that many block rows in shared memory for the whole solve
   size_t smem_pcg = 0;
-  int pcg_threads = 256;
+  int pcg_threads = 512;  // measured on config 5 (profiles/r02f_pcg_geometry_sweep.txt): 512 x 148..296 CTAs 0.231 ms per LM iteration, 256 x 296 0.240
   bool with_F = false;
   // pass A (camera-major F'F): block codes grouped by image, split into chunks
   DBuf<int32_t> citems, chunk_cam, chunk_beg;

@@ -121,7 +121,7 @@ inline int run_build(mvba_problem* h, const mvba_solve_options& o, double radius
   s->build_launches++;
   if (mode == 0 && h->nranks > 1 && v.P > 0) {  // this rank's landmark-part gradient maximum, into its own slot of the summed buffer
     const int64_t ne = 3 * (int64_t)v.P;
-    gradmax_kernel<<<(unsigned)((ne + 255) / 256), 256, 0, h->stream>>>(0, ne, nullptr, s->ge.p, nullptr, a.jscale_e, nullptr, 0,
+    gradmax_kernel<<<(unsigned)std::max<int64_t>(1, std::min<int64_t>((ne + 255) / 256, (int64_t)8 * h->sm_count)), 256, 0, h->stream>>>(0, ne, nullptr, s->ge.p, nullptr, a.jscale_e, nullptr, 0,
                                                                          s->red.p + s->o_gmaxe + h->rank);
     h->launches++;
   }
@@ -299,7 +299,7 @@ inline int solver_solve(mvba_problem* h, const mvba_solve_options& o, mvba_summa
       gradmax_kernel<<<(unsigned)((s->nf + h->nranks + tb - 1) / tb), tb, 0, h->stream>>>(s->nf, 0, s->R.g, nullptr, scaled ? s->jscale_f.p : nullptr, nullptr,
                                                                                          s->red.p + s->o_gmaxe, h->nranks, s->lm.p + LM_GMAX);
     else
-      gradmax_kernel<<<(unsigned)((s->nf + ne + tb - 1) / tb), tb, 0, h->stream>>>(s->nf, ne, s->R.g, s->ge.p, scaled ? s->jscale_f.p : nullptr,
+      gradmax_kernel<<<(unsigned)std::max<int64_t>(1, std::min<int64_t>((s->nf + ne + tb - 1) / tb, (int64_t)8 * h->sm_count)), tb, 0, h->stream>>>(s->nf, ne, s->R.g, s->ge.p, scaled ? s->jscale_f.p : nullptr,
                                                                                     scaled ? s->jscale_e.p : nullptr, nullptr, 0, s->lm.p + LM_GMAX);
     h->launches++;
     if (s->nf) {
@@ -344,7 +344,7 @@ inline int solver_solve(mvba_problem* h, const mvba_solve_options& o, mvba_summa
       else backsub_kernel<false, true><<<s->grid_backsub, 128, 0, h->stream>>>(v, b);  // R kept in registers: the kernel is bound by L1 requests (measured: 0.02 ms per iteration)
       h->launches += 2;
     }
-    update_kernel<<<(v.nx + tb - 1) / tb, tb, 0, h->stream>>>(v.nx, s->nf, s->xcol.p, h->d_x.p, s->y.p, s->ye.p, scaled ? s->jscale_f.p : nullptr,
+    update_kernel<<<(unsigned)std::max<int64_t>(1, std::min<int64_t>((v.nx + tb - 1) / tb, (int64_t)8 * h->sm_count)), tb, 0, h->stream>>>(v.nx, s->nf, s->xcol.p, h->d_x.p, s->y.p, s->ye.p, scaled ? s->jscale_f.p : nullptr,
                                                               scaled ? s->jscale_e.p : nullptr, h->bounded ? s->lo.p : nullptr,
                                                               h->bounded ? s->hi.p : nullptr, h->d_xnew.p, s->lm.p);
     h->launches++;
