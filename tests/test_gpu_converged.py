@@ -6,8 +6,9 @@ scale floating; every intrinsic floating on ragged tracks; floating time offsets
 the stay-near-initial landmark prior of the reference (XYZError with --tri_weight, rig_calibrator.cc:1886-1901) pins the
 7-dof gauge, there are no gross outliers, max_trust_region_radius = 1e7 keeps the LM damping from vanishing along the
 quaternion-norm null directions (the reference has no manifold, dense_map_utils.cc:171-178) -- and both sides iterate with
-an almost exact Newton step (eta = 1e-8) for 60 iterations, by which point the cost moves by less than 1e-8 relative per
-iteration.  tests/test_oracle_converged.py (CPU) shows that this state is path independent at the tolerances used here:
+an almost exact Newton step (eta = 1e-8) for at most 120 iterations: both stop on the function tolerance after 60 to 90
+(at 60 the cost still moves by 1e-9 relative per iteration and two oracle runs on 8 threads were seen 8.7e-7 apart in a pose;
+at the tolerance stop they are within 3e-9).  tests/test_oracle_converged.py (CPU) shows that this state is path independent at the tolerances used here:
 the oracle on 1 and on 8 threads (different summation orders, different CG iteration counts) agree to 5e-7 in the poses
 (typically 1e-9) and to 5e-5 px in the intrinsics.
 
@@ -30,7 +31,7 @@ from test_gpu_parity_solve import CASES, _param_error
 pytestmark = pytest.mark.gpu
 
 FAMILIES = ("depth_mesh", "rig3_ragged_intr", "offsets")
-OPTS = dict(max_num_iterations=60, eta=1e-8, max_trust_region_radius=1e7)
+OPTS = dict(max_num_iterations=120, eta=1e-8, max_trust_region_radius=1e7)
 INTRINSIC = ("focal", "center", "distortion")
 
 
