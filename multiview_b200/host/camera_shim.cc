@@ -8,6 +8,8 @@
 #include "pose_math.h"
 #include "bracket.h"
 #include "residual_stats.h"
+#include "cli_flags.h"
+#include "ply_io.h"
 
 static thread_local std::string g_cam_err;
 
@@ -169,5 +171,44 @@ int mvh_update_rpc_undistortion(const int* size, const double* focal, const doub
     for (int i = 0; i < nd; i++) dist[i] = d[(size_t)i];
     return 0;
   } catch (const std::exception& e) { g_cam_err = e.what(); return -1; }
+}
+// ---- tests/test_cli.py ----
+// read_ply: counts, then (when the buffers are large enough) the arrays
+int mvh_read_ply(const char* path, long long cap_vertices, float* vertices, long long cap_faces, unsigned* faces, long long* num_vertices, long long* num_faces) {
+  try {
+    mvba_host::TriangleMesh m = mvba_host::read_ply(path);
+    *num_vertices = (long long)m.vertices.size() / 3; *num_faces = (long long)m.faces.size() / 3;
+    if (*num_vertices <= cap_vertices && vertices) std::memcpy(vertices, m.vertices.data(), m.vertices.size() * sizeof(float));
+    if (*num_faces <= cap_faces && faces) std::memcpy(faces, m.faces.data(), m.faces.size() * sizeof(unsigned));
+    return 0;
+  } catch (const std::exception& e) { g_cam_err = e.what(); return -1; }
+}
+// calc_rig_using_word_to_cam; world_to_cam as 12 doubles per image (R row-major, t), out_ref_to_cam 12 per sensor
+int mvh_rig_from_poses(int num_sensors, int num_cameras, const int* cam_sensor, const int* beg, const int* end, const double* cam_stamp,
+                       const double* ref_stamps, const double* world_to_ref7, const double* world_to_cam12, const double* offsets, double* out_ref_to_cam12) {
+  try {
+    std::vector<mvba_host::Affine> w2c((size_t)num_cameras);
+    for (int c = 0; c < num_cameras; c++) std::memcpy(w2c[c].data(), world_to_cam12 + 12 * (size_t)c, 12 * sizeof(double));
+    auto r = mvba_host::calc_rig_using_world_to_cam(num_sensors, num_cameras, cam_sensor, beg, end, cam_stamp, ref_stamps, world_to_ref7, w2c, offsets);
+    for (int t = 0; t < num_sensors; t++) std::memcpy(out_ref_to_cam12 + 12 * (size_t)t, r[t].data(), 12 * sizeof(double));
+    return 0;
+  } catch (const std::exception& e) { g_cam_err = e.what(); return -1; }
+}
+// the flag table as text: one "name type default" line per flag, in declaration order
+int mvh_flag_table(char* out, int cap) {
+  mvba_host::Flags f;
+  std::string s;
+  for (const mvba_host::FlagSpec& k : mvba_host::flag_table()) {
+    const char* base = reinterpret_cast<const char*>(&f) + k.offset;
+    std::string v;
+    if (k.type == 'd') v = mvba_host::format_double(*reinterpret_cast<const double*>(base));
+    else if (k.type == 'i') v = std::to_string(*reinterpret_cast<const int*>(base));
+    else if (k.type == 'b') v = *reinterpret_cast<const bool*>(base) ? "true" : "false";
+    else v = "\"" + *reinterpret_cast<const std::string*>(base) + "\"";
+    s += std::string(k.name) + " " + k.type + " " + v + "\n";
+  }
+  if ((int)s.size() + 1 > cap) return -1;
+  std::memcpy(out, s.c_str(), s.size() + 1);
+  return (int)mvba_host::flag_table().size();
 }
 }

@@ -9,6 +9,7 @@
 #include <cmath>
 #include <limits>
 #include <stdexcept>
+#include <string>
 #include <vector>
 
 #include "rig_io.h"
@@ -83,6 +84,47 @@ inline std::vector<Affine> world_to_cam_all(int num_cameras, const int* cam_sens
     const int t = cam_sensor[c];
     out[c] = calc_world_to_cam(world_to_ref + 7 * beg[c], world_to_ref + 7 * end[c], ref_to_cam + 7 * t, ref_stamps[beg[c]], ref_stamps[end[c]],
                                offsets[t], cam_stamp[c]);
+  }
+  return out;
+}
+
+// Eigen::Affine3d::inverse() (Affine mode: general inverse of the 3x3 part, t' = -L^-1 t)
+inline Affine inverse(const Affine& A) {
+  const double a = A[0], b = A[1], c = A[2], d = A[3], e = A[4], f = A[5], g = A[6], h = A[7], i = A[8];
+  const double det = a * (e * i - f * h) - b * (d * i - f * g) + c * (d * h - e * g);
+  Affine B;
+  B[0] = (e * i - f * h) / det; B[1] = (c * h - b * i) / det; B[2] = (b * f - c * e) / det;
+  B[3] = (f * g - d * i) / det; B[4] = (a * i - c * g) / det; B[5] = (c * d - a * f) / det;
+  B[6] = (d * h - e * g) / det; B[7] = (b * g - a * h) / det; B[8] = (a * e - b * d) / det;
+  for (int r = 0; r < 3; r++) B[9 + r] = -(B[3 * r] * A[9] + B[3 * r + 1] * A[10] + B[3 * r + 2] * A[11]);
+  return B;
+}
+
+// calc_rig_using_word_to_cam, rig_calibrator.cc:1190-1262: the rig transforms when --use_initial_rig_transforms is off.  Per image
+// ref_to_cam = world_to_cam * interp(world_to_ref)^-1 (identity for the reference sensor); per sensor and per matrix entry the
+// MIDDLE element of that list in image order (vals[vals.size() / 2]: the reference calls it a median but does not sort), then the
+// 3x3 part is divided by the cube root of its determinant.  Throws where the reference aborts (a sensor without images).
+inline std::vector<Affine> calc_rig_using_world_to_cam(int num_sensors, int num_cameras, const int* cam_sensor, const int* beg, const int* end,
+                                                       const double* cam_stamp, const double* ref_stamps, const double* world_to_ref,
+                                                       const std::vector<Affine>& world_to_cam, const double* offsets) {
+  if ((size_t)num_cameras != world_to_cam.size()) throw std::runtime_error("There must be as many world to cam transforms as metadata sets for them.\n");
+  std::vector<std::vector<Affine>> per(num_sensors);
+  double ident7[7] = {0, 0, 0, 0, 0, 0, 1};
+  for (int c = 0; c < num_cameras; c++) {
+    const int t = cam_sensor[c];
+    if (t == 0) { per[t].push_back(identity_affine()); continue; }
+    const Affine w2r = calc_world_to_cam(world_to_ref + 7 * beg[c], world_to_ref + 7 * end[c], ident7, ref_stamps[beg[c]], ref_stamps[end[c]],
+                                         offsets[t], cam_stamp[c]);
+    per[t].push_back(compose(world_to_cam[c], inverse(w2r)));
+  }
+  std::vector<Affine> out(num_sensors);
+  for (int t = 0; t < num_sensors; t++) {
+    if (per[t].empty()) throw std::runtime_error("No poses were found for rig sensor with id: " + std::to_string(t) + "\n");
+    Affine m = per[t][per[t].size() / 2];   // entry by entry the same element
+    const double det = m[0] * (m[4] * m[8] - m[5] * m[7]) - m[1] * (m[3] * m[8] - m[5] * m[6]) + m[2] * (m[3] * m[7] - m[4] * m[6]);
+    const double s = std::pow(det, 1.0 / 3.0);
+    for (int k = 0; k < 9; k++) m[k] /= s;
+    out[t] = m;
   }
   return out;
 }

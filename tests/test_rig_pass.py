@@ -1,4 +1,4 @@
-"""examples/rig_pass.cc, the stand-alone driver, on a CPU box: a synthetic rig is written out as rig_config.txt + NVM (image paths
+"""examples/rig_calibrator.cc, the stand-alone driver with the reference's command line, on a CPU box: a synthetic rig is written out as rig_config.txt + NVM (image paths
 carrying sensor and timestamp), the driver reads them back, brackets the images and assembles the pass; --dry_run prints it before
 the first device call.  The assembled arrays must be the synthetic problem's own.  Without --dry_run on a box with no GPU the
 driver must fail loudly at the first compute call (no CPU fallback)."""
@@ -62,10 +62,10 @@ def dataset(tmp_path_factory):
     return d, pr
 
 
-def run(d, *extra):
-    exe = os.path.join(ROOT, "examples", "rig_pass")
-    return subprocess.run([exe, "--rig_config", str(d / "rig_config.txt"), "--nvm", str(d / "map.nvm"), "--out_dir", str(d), *extra],
-                          capture_output=True, text=True, timeout=300)
+def run(d, *extra, cwd=None):
+    exe = os.path.join(ROOT, "examples", "rig_calibrator")
+    return subprocess.run([exe, "--rig_config", str(d / "rig_config.txt"), "--nvm", str(d / "map.nvm"), "--out_dir", str(d / "out"), *extra],
+                          capture_output=True, text=True, timeout=300, cwd=cwd)
 
 
 def test_dry_run_assembles_the_synthetic_pass(dataset):
@@ -102,7 +102,9 @@ def test_the_assembled_pass_runs_on_the_device_and_follows_the_oracle_driven_pas
     (rig_calibrator.cc:1550-1985).  The NVM stores keypoints as text relative to the optical centre, so the driver's pixels
     differ from the problem's by float32 round-off (< 1e-4 px): costs are compared to 1e-4 relative, poses to 1e-5."""
     d, pr = dataset
-    out = run(d, "--bracket_len", "1.0", "--num_passes", "2", "--num_iterations", "10", "--float_rig")
+    names = [s.name for s in pr.sensors]
+    out = run(d, "--bracket_len", "1.0", "--calibrator_num_passes", "2", "--num_iterations", "10", "--use_initial_rig_transforms",
+              "--rig_transforms_to_float", " ".join(names[1:]), "--camera_poses_to_float", names[0], "--min_triangulation_angle", "0.01")
     assert out.returncode == 0, out.stderr + out.stdout[-2000:]
     text = out.stdout
     assert text.count("The 25, 50, 75, and 100th percentile residual stats before opt") == 2
@@ -136,9 +138,129 @@ def test_the_assembled_pass_runs_on_the_device_and_follows_the_oracle_driven_pas
         assert abs(g[2] - w[2]) <= 1e-4 * w[2] and abs(g[3] - w[3]) <= 1e-4 * w[3], (g, w)
     # ---- written camera list: world_to_cam of every image at the optimised parameters ----
     Rm, tv = synth.world_to_cam_all(pr)
-    rows = [l.split() for l in (d / "cameras.txt").read_text().splitlines() if l and not l.startswith("#")]
+    rows = [l.split() for l in (d / "out" / "cameras.txt").read_text().splitlines() if l and not l.startswith("#")]
+    assert (d / "out" / "rig_config.txt").exists() and not (d / "out" / "cameras.nvm").exists()       # the NVM only with --save_nvm
     files = [f"data/{pr.sensors[pr.cam_sensor[c]].name}/{g17(pr.cam_stamp[c])}.jpg" for c in range(len(pr.cam_sensor))]
     by_file = {r[0]: np.array(r[1:], float) for r in rows}
     for c, f in enumerate(files):
         m = by_file[f]
         assert np.abs(m[:9] - Rm[c].ravel()).max() <= 1e-5 and np.abs(m[9:12] - tv[c]).max() <= 1e-5, f
+
+
+@pytest.mark.gpu
+def test_the_flags_reach_the_solver(dataset, oracle_lib):
+    """One pass with the reference's 'what floats' flags and the stay-near-the-triangulation prior: reference-sensor poses, ONE rig
+    transform, one focal length and the time offsets float (rig_calibrator.cc:1702-1752), --tri_weight adds an XYZError per track
+    with an inlier feature against the pass's own triangulation (:1571-1580, 1886-1901).  The oracle solves the same pass
+    assembled by hand from the synthetic problem."""
+    d, _ = dataset
+    pr = synth.make_problem(seed=31, sensors="rig3", num_ref=10, num_landmarks=120, obs_per_track=5)     # as the files were written
+    names = [s.name for s in pr.sensors]
+    out = run(d, "--bracket_len", "1.0", "--calibrator_num_passes", "1", "--num_iterations", "2", "--use_initial_rig_transforms",
+              "--camera_poses_to_float", names[0], "--rig_transforms_to_float", names[1], "--intrinsics_to_float", f"{names[2]}:focal_length",
+              "--float_timestamp_offsets", "--tri_weight", "0.5", "--tri_robust_threshold", "0.1", "--min_triangulation_angle", "0.01", "--save_nvm")
+    assert out.returncode == 0, out.stderr + out.stdout[-2000:]
+    assert "tri_x_m: " in out.stdout and (d / "out" / "cameras.nvm").exists()
+    import re
+    m = re.search(r"pass 0: (\d+) inlier features, cost (\S+) -> (\S+) in", out.stdout)
+    got = (int(m.group(1)), float(m.group(2)), float(m.group(3)))
+    T = len(pr.sensors)
+    u8 = lambda v: np.array(v, np.uint8)
+    pr.float_poses = u8([1, 0, 0]); pr.float_rig = u8([0, 1, 0]); pr.float_focal = u8([0, 0, 1]); pr.float_center = u8([0] * T); pr.float_dist = u8([0] * T)
+    pr.float_offsets = True
+    img = np.array([[s.width, s.height] for s in pr.sensors], np.float64)
+    o_all = _abi.Binding(oracle_lib, "oracle_", pr)
+    inl = o_all.flag_exclusion(img, img)
+    xyz, inl = o_all.triangulate(inl, pr.xyz)
+    o_all.close()
+    pr.xyz[:] = xyz.ravel()
+    q = pr.keep_observations(inl == 1)
+    pids = np.unique(q.pid).astype(np.int32)
+    q.priors = {synth.BLOCK_TRI: (pids, xyz.reshape(-1, 3)[pids].reshape(-1).copy(), 0.5, 0.1)}
+    o = _abi.Binding(oracle_lib, "oracle_", q)
+    s, _ = o.solve(_abi.default_options(max_num_iterations=2), jac_mode=1, num_threads=1)
+    o.close()
+    assert got[0] == int((inl == 1).sum())
+    assert abs(got[1] - s.initial_cost) <= 1e-4 * s.initial_cost and abs(got[2] - s.final_cost) <= 1e-4 * s.final_cost, (got, s.initial_cost, s.final_cost)
+    # the written rig: only the floated transform and the floated focal length moved
+    rig_in = (d / "rig_config.txt").read_text().split("\n\n")
+    rig_out = (d / "out" / "rig_config.txt").read_text().split("\n\n")
+    field = lambda blk, key: [l for l in blk.splitlines() if l.startswith(key)][0]
+    assert field(rig_out[2], "focal_length:") == field(rig_in[2], "focal_length:")
+    assert field(rig_out[3], "focal_length:") != field(rig_in[3], "focal_length:")
+
+
+def depth_and_mesh_inputs(d, pr):
+    """Depth clouds (<image stem>.pc, readXyzImage's layout: rows, cols, channels as int32, then float32 xyz per pixel) for the
+    images of sensor 1, holding the camera-frame position of every feature at the initial state, and a box mesh around the scene."""
+    import struct
+    from test_mesh import scene_box
+    Rm, tv = synth.world_to_cam_all(pr)
+    _, Xc = synth.project(pr, Rm, tv, pr.xyz, pr.pid, pr.cid)
+    s1 = pr.sensors[1]
+    W, H = int(s1.width), int(s1.height)
+    clouds = {}
+    px = pr.pix.reshape(-1, 2)
+    for i in np.nonzero(pr.cam_sensor[pr.cid] == 1)[0]:
+        col, row = int(np.round(px[i, 0])), int(np.round(px[i, 1]))     # np.round and std::round differ only at exact .5 of a float32 pixel
+        assert 0 <= col < W and 0 <= row < H
+        clouds.setdefault(int(pr.cid[i]), np.zeros((H, W, 3), np.float32))[row, col] = Xc[i].astype(np.float32)
+    os.makedirs(d / "data" / pr.sensors[1].name, exist_ok=True)
+    for c, img in clouds.items():
+        with open(d / "data" / pr.sensors[1].name / (g17(pr.cam_stamp[c]) + ".pc"), "wb") as f:
+            f.write(struct.pack("<iii", H, W, 3)); f.write(img.tobytes())
+    has = np.zeros(pr.num_obs, np.uint8); dxyz = np.zeros((pr.num_obs, 3), np.float32)
+    for i in np.nonzero(pr.cam_sensor[pr.cid] == 1)[0]:
+        v = clouds[int(pr.cid[i])][int(np.round(px[i, 1])), int(np.round(px[i, 0]))]
+        if np.any(v != 0):
+            has[i] = 1; dxyz[i] = v
+    (v, f), _, _ = scene_box(pr, 6)
+    with open(d / "box.ply", "wb") as fh:
+        fh.write((f"ply\nformat binary_little_endian 1.0\nelement vertex {len(v)}\nproperty float x\nproperty float y\nproperty float z\n"
+                  f"element face {len(f)}\nproperty list uchar int vertex_indices\nend_header\n").encode())
+        fh.write(v.astype("<f4").tobytes())
+        for tri in f:
+            fh.write(struct.pack("<Biii", 3, *[int(k) for k in tri]))
+    return has, dxyz, v, f
+
+
+@pytest.mark.gpu
+def test_mesh_and_depth_flags(dataset, oracle_lib):
+    """--mesh (a .ply read by the driver, rays intersected on the device), depth clouds found beside the images, --depth_tri_weight,
+    --depth_mesh_weight, --mesh_tri_weight, --depth_to_image_transforms_to_float and --float_scale: one pass against the oracle
+    driven by hand through the same steps (rig_calibrator.cc:1582-1589, 1755-1840, 1857-1883)."""
+    d, _ = dataset
+    pr = synth.make_problem(seed=31, sensors="rig3", num_ref=10, num_landmarks=120, obs_per_track=5)
+    names = [s.name for s in pr.sensors]
+    has, dxyz, verts, faces = depth_and_mesh_inputs(d, pr)
+    out = run(d, "--bracket_len", "1.0", "--calibrator_num_passes", "1", "--num_iterations", "4", "--use_initial_rig_transforms",
+              "--camera_poses_to_float", names[0], "--rig_transforms_to_float", " ".join(names[1:]), "--mesh", str(d / "box.ply"),
+              "--depth_tri_weight", "200", "--depth_mesh_weight", "20", "--mesh_tri_weight", "10", "--depth_to_image_transforms_to_float", names[1],
+              "--float_scale", "--min_triangulation_angle", "0.01", "--max_ray_dist", "50", cwd=str(d))
+    assert out.returncode == 0, out.stderr + out.stdout[-2000:]
+    for tag in ("depth_tri_x_m: ", "depth_mesh_x_m: ", "mesh_tri_x_m: "):
+        assert tag in out.stdout, tag
+    import re
+    m = re.search(r"pass 0: (\d+) inlier features, cost (\S+) -> (\S+) in", out.stdout)
+    got = (int(m.group(1)), float(m.group(2)), float(m.group(3)))
+    T = len(pr.sensors)
+    u8 = lambda v: np.array(v, np.uint8)
+    pr.float_poses = u8([1, 0, 0]); pr.float_rig = u8([0, 1, 1]); pr.float_d2i = u8([0, 1, 0]); pr.float_scale = True
+    pr.depth_tri_weight = 200.0; pr.depth_mesh_weight = 20.0
+    img = np.array([[s.width, s.height] for s in pr.sensors], np.float64)
+    o_all = _abi.Binding(oracle_lib, "oracle_", pr)
+    inl = o_all.flag_exclusion(img, img)
+    xyz, inl = o_all.triangulate(inl, pr.xyz)
+    pr.xyz[:] = xyz.ravel()
+    hm, mxyz, pmesh = o_all.mesh_intersect(verts, faces, 0.0, 50.0, inl)
+    o_all.close()
+    pr.has_depth = has; pr.depth_xyz = dxyz.reshape(-1).copy(); pr.has_mesh = hm; pr.mesh_xyz = mxyz.reshape(-1).copy()
+    q = pr.keep_observations(inl == 1)
+    pids = np.unique(q.pid).astype(np.int32)
+    pids = pids[~np.all(pmesh[pids] == 1e100, axis=1)]
+    q.priors = {synth.BLOCK_MESH_TRI: (pids, pmesh[pids].reshape(-1).copy(), 10.0, pr.robust_threshold)}
+    o = _abi.Binding(oracle_lib, "oracle_", q)
+    s, _ = o.solve(_abi.default_options(max_num_iterations=4), jac_mode=1, num_threads=1)
+    o.close()
+    assert got[0] == int((inl == 1).sum())
+    assert abs(got[1] - s.initial_cost) <= 1e-4 * s.initial_cost and abs(got[2] - s.final_cost) <= 1e-4 * s.final_cost, (got, s.initial_cost, s.final_cost)
