@@ -8,12 +8,19 @@
 //   DistortCentered / UndistortCentered  camera_params.cc:260-355 (radtan undistortion: the five fixed-point
 //                  iterations of cv::undistortPoints, which is what the reference calls)
 //   RPC            rpc_distortion.cc:116-160, 272-293 (distortion half, then undistortion half)
-// Not mirrored: the OpenCV calibration-file constructor, GenerateRemapMaps (cv::Mat), updateRpcUndistortion (the RPC
-// fit).
+//   calibration-file constructor  camera_params.cc:50-104 (cv::FileStorage there; here a reader of the same YAML files:
+//                  scalars and !!opencv-matrix nodes with dt: d / f / i, which is what OpenCV writes for these keys)
+//   GenerateRemapMaps  camera_params.cc:361-371 (cv::Mat CV_32FC2 there; here rows x cols interleaved float pairs)
+//   updateRpcUndistortion  camera_params.cc:214-254, defined in rpc_pairs.h (the fit is SURVEY.md 8(f) N4, on the device)
 #pragma once
 #include <cmath>
 #include <cstdint>
+#include <cstdlib>
+#include <fstream>
+#include <map>
+#include <sstream>
 #include <stdexcept>
+#include <string>
 #include <vector>
 
 namespace camera {
@@ -69,6 +76,51 @@ class CameraParameters {
     optical_offset_ = optical_center;
     crop_offset_ = Vector2i(0, 0);
     SetDistortion(distortion);
+  }
+
+  // camera_params.cc:50-104: an OpenCV calibration file (YAML).  Keys with their fall-backs, in the reference's order: width / height
+  // (image_width / image_height), intrinsic_matrix (camera_matrix), distortion (distortion_coefficients), undistorted_width /
+  // undistorted_height (default: the distorted size), crop_x / crop_y (default 0).
+  explicit CameraParameters(std::string const& calibration_file, std::string const& base_dir = "") {
+    std::ifstream f(calibration_file);
+    if (!f.good() && base_dir != "") f.open(base_dir + "/" + calibration_file);   // it may be relative to the map file's directory
+    if (!f.good()) throw std::runtime_error("Calibration file does not exist: " + calibration_file);
+    std::map<std::string, double> scalars;
+    std::map<std::string, std::vector<double>> matrices;
+    std::map<std::string, std::pair<int, int>> shapes;
+    read_opencv_yaml(f, scalars, matrices, shapes);
+    auto scalar = [&](const char* k) { auto it = scalars.find(k); return it == scalars.end() ? 0 : (int)it->second; };
+    Vector2i size(scalar("width"), scalar("height"));
+    if (size[0] == 0 || size[1] == 0) size = Vector2i(scalar("image_width"), scalar("image_height"));
+    SetDistortedSize(size);
+    SetDistortedCropSize(size);
+    const char* km = matrices.count("intrinsic_matrix") && !matrices["intrinsic_matrix"].empty() ? "intrinsic_matrix" : "camera_matrix";
+    if (!matrices.count(km) || shapes[km].first < 2 || shapes[km].second < 3) throw std::runtime_error("No camera matrix in calibration file: " + calibration_file);
+    const std::vector<double>& K = matrices[km];
+    const int kc = shapes[km].second;
+    optical_offset_ = Vector2d(K[2], K[kc + 2]);
+    focal_length_ = Vector2d(K[0], K[kc + 1]);
+    const char* kd = matrices.count("distortion") && !matrices["distortion"].empty() ? "distortion" : "distortion_coefficients";
+    SetDistortion(matrices.count(kd) ? matrices[kd] : std::vector<double>());
+    size = Vector2i(scalar("undistorted_width"), scalar("undistorted_height"));
+    if (!(size[0] > 0 && size[1] > 0)) size = distorted_image_size_;
+    SetUndistortedSize(size);
+    crop_offset_ = Vector2i(scalar("crop_x"), scalar("crop_y"));
+  }
+
+  // camera_params.cc:361-371: for every pixel of the (scaled) undistorted image the distorted-image position it samples,
+  // the map cv::remap takes.  remap_map holds rows x cols pairs (x, y) as float32, row-major, like the reference's CV_32FC2 matrix;
+  // rows = int(scale * undistorted height), cols = int(scale * undistorted width) (cv::Mat::create truncates the same way).
+  void GenerateRemapMaps(std::vector<float>* remap_map, int* rows, int* cols, double scale = 1.0) const {
+    *rows = (int)(scale * undistorted_image_size_[1]); *cols = (int)(scale * undistorted_image_size_[0]);
+    remap_map->assign(2 * (size_t)*rows * (size_t)*cols, 0.0f);
+    Vector2d distorted;
+    for (int y = 0; y < *rows; y++)
+      for (int x = 0; x < *cols; x++) {
+        Convert<UNDISTORTED, DISTORTED>(Vector2d(x / scale, y / scale), &distorted);
+        (*remap_map)[2 * ((size_t)y * *cols + x)] = (float)(scale * distorted[0]);
+        (*remap_map)[2 * ((size_t)y * *cols + x) + 1] = (float)(scale * distorted[1]);
+      }
   }
 
   template <int SRC, int DEST> void Convert(Vector2d const& input, Vector2d* output) const {
@@ -159,6 +211,42 @@ class CameraParameters {
   }
 
  private:
+  // The subset of OpenCV's YAML persistence these files use: "key: number" and
+  //   key: !!opencv-matrix / rows: R / cols: C / dt: d / data: [ v, v, ... ]  (the data list may span lines).
+  static void read_opencv_yaml(std::istream& in, std::map<std::string, double>& scalars, std::map<std::string, std::vector<double>>& matrices,
+                               std::map<std::string, std::pair<int, int>>& shapes) {
+    std::string line, current;
+    bool in_data = false;
+    auto numbers = [](std::string text, std::vector<double>& out) {
+      for (char& c : text) if (c == ',' || c == '[' || c == ']') c = ' ';
+      std::istringstream ss(text);
+      std::string tok;
+      while (ss >> tok) { char* end = nullptr; const double v = std::strtod(tok.c_str(), &end); if (end != tok.c_str()) out.push_back(v); }
+    };
+    while (std::getline(in, line)) {
+      if (!line.empty() && line.back() == '\r') line.pop_back();
+      if (line.empty() || line[0] == '%' || line.rfind("---", 0) == 0) continue;
+      if (in_data) { numbers(line, matrices[current]); if (line.find(']') != std::string::npos) in_data = false; continue; }
+      const size_t colon = line.find(':');
+      if (colon == std::string::npos) continue;
+      const size_t k0 = line.find_first_not_of(" \t");
+      std::string key = line.substr(k0, colon - k0), val = line.substr(colon + 1);
+      const size_t v0 = val.find_first_not_of(" \t");
+      val = v0 == std::string::npos ? "" : val.substr(v0);
+      if (k0 == 0 && val.rfind("!!opencv-matrix", 0) == 0) { current = key; matrices[current].clear(); shapes[current] = {0, 0}; continue; }
+      if (k0 > 0 && !current.empty()) {   // a field of the current matrix node
+        if (key == "rows") shapes[current].first = std::atoi(val.c_str());
+        else if (key == "cols") shapes[current].second = std::atoi(val.c_str());
+        else if (key == "data") { numbers(val, matrices[current]); in_data = val.find(']') == std::string::npos; }
+        continue;
+      }
+      current.clear();
+      char* end = nullptr;
+      const double v = std::strtod(val.c_str(), &end);
+      if (end != val.c_str()) scalars[key] = v;
+    }
+  }
+
   void DistortCentered(Vector2d const& u, Vector2d* out) const {
     const size_t n = distortion_coeffs_.size();
     const Vector2d shift = optical_offset_ - distorted_half_size_;

@@ -211,4 +211,32 @@ int mvh_flag_table(char* out, int cap) {
   std::memcpy(out, s.c_str(), s.size() + 1);
   return (int)mvba_host::flag_table().size();
 }
+// ---- tests/test_camera_params.py: the calibration-file constructor and GenerateRemapMaps ----
+// out16: width height crop_w crop_h undist_w undist_h crop_x crop_y fx fy cx cy nd, then up to 3 distortion values are not enough: dist
+// receives GetDistortion() (cap_dist values at most)
+int mvh_camera_from_file(const char* file, const char* base_dir, double* out13, double* dist, int cap_dist) {
+  try {
+    camera::CameraParameters cp(std::string(file), std::string(base_dir ? base_dir : ""));
+    const camera::Vector2i a = cp.GetDistortedSize(), b = cp.GetDistortedCropSize(), c = cp.GetUndistortedSize(), d = cp.GetCropOffset();
+    const camera::Vector2d f = cp.GetFocalVector(), o = cp.GetOpticalOffset();
+    const double v[13] = {(double)a[0], (double)a[1], (double)b[0], (double)b[1], (double)c[0], (double)c[1], (double)d[0], (double)d[1], f[0], f[1], o[0], o[1],
+                          (double)cp.GetDistortion().size()};
+    std::memcpy(out13, v, sizeof(v));
+    for (size_t i = 0; i < cp.GetDistortion().size() && (int)i < cap_dist; i++) dist[i] = cp.GetDistortion()[i];
+    return 0;
+  } catch (const std::exception& e) { g_cam_err = e.what(); return -1; }
+}
+int mvh_generate_remap_maps(const int* size, const double* focal, const double* center, const double* dist, int nd, const int* undist_size, double scale,
+                            float* map, long long cap_pairs, int* rows, int* cols) {
+  try {
+    using namespace camera;
+    CameraParameters cp(Vector2i(size[0], size[1]), Vector2d(focal[0], focal[1]), Vector2d(center[0], center[1]), std::vector<double>(dist, dist + nd));
+    if (undist_size) cp.SetUndistortedSize(Vector2i(undist_size[0], undist_size[1]));
+    std::vector<float> m;
+    cp.GenerateRemapMaps(&m, rows, cols, scale);
+    if ((long long)m.size() / 2 > cap_pairs) { g_cam_err = "map buffer too small"; return -1; }
+    std::memcpy(map, m.data(), m.size() * sizeof(float));
+    return 0;
+  } catch (const std::exception& e) { g_cam_err = e.what(); return -1; }
+}
 }

@@ -183,3 +183,62 @@ def test_host_pose_math_matches_scipy_golden_and_flags_bad_brackets(host):
         host.mvh_rigid_roundtrip(scaled.ctypes.data_as(dp), back.ctypes.data_as(dp))
         s = np.sign(back[3:] @ a[3:])
         assert np.abs(back[:3] - a[:3]).max() == 0 and np.abs(s * back[3:] - a[3:]).max() < 1e-14
+
+
+def camera_from_file(lib, path, base_dir=""):
+    out = np.zeros(13); dist = np.zeros(128)
+    rc = lib.mvh_camera_from_file(str(path).encode(), base_dir.encode(), out.ctypes.data_as(dp), dist.ctypes.data_as(dp), 128)
+    if rc != 0:
+        raise RuntimeError(lib.mvh_camera_last_error().decode())
+    return out, dist[:int(out[12])]
+
+
+def test_calibration_file_constructor(host, tmp_path):
+    """CameraParameters(calibration_file, base_dir), camera_params.cc:50-104: a file written by cv::FileStorage itself (the reference
+    reads it with cv::FileStorage), then the fall-back key names in the layout OpenCV's calibration tool writes, the default
+    undistorted size and crop, the base_dir fall-back and the missing-file error."""
+    cv2 = pytest.importorskip("cv2")
+    K = np.array([[608.25, 0, 640.5], [0, 607.75, 480.125], [0, 0, 1]])
+    dist = np.array([[-0.25, 0.08, 0.0012, -0.0008, 0.011]])
+    p = tmp_path / "cam.yml"
+    fs = cv2.FileStorage(str(p), cv2.FILE_STORAGE_WRITE)
+    for k, v in (("width", 1280), ("height", 960), ("undistorted_width", 1500), ("undistorted_height", 1100), ("crop_x", 12), ("crop_y", 7)):
+        fs.write(k, v)
+    fs.write("intrinsic_matrix", K); fs.write("distortion", dist)
+    fs.release()
+    out, d = camera_from_file(host, p)
+    assert list(out[:8]) == [1280, 960, 1280, 960, 1500, 1100, 12, 7]
+    assert list(out[8:12]) == [608.25, 607.75, 640.5, 480.125] and np.array_equal(d, dist.ravel())
+    q = tmp_path / "calib.yaml"
+    q.write_text("%YAML:1.0\n---\nimage_width: 224\nimage_height: 171\ncamera_matrix: !!opencv-matrix\n   rows: 3\n   cols: 3\n   dt: d\n"
+                 "   data: [ 2.1000000000000000e+02, 0., 1.1230000000000000e+02, 0.,\n       2.0950000000000000e+02, 8.5099999999999994e+01, 0., 0., 1. ]\n"
+                 "distortion_coefficients: !!opencv-matrix\n   rows: 1\n   cols: 1\n   dt: d\n   data: [ 9.9800000000000000e-01 ]\n")
+    out, d = camera_from_file(host, q)
+    assert list(out[:8]) == [224, 171, 224, 171, 224, 171, 0, 0]          # undistorted size defaults to the distorted one, crop to zero
+    assert list(out[8:12]) == [210.0, 209.5, 112.3, 85.1] and list(d) == [0.998]
+    out2, _ = camera_from_file(host, "calib.yaml", str(tmp_path))          # relative to the map file's directory
+    assert np.array_equal(out, out2)
+    with pytest.raises(RuntimeError, match="Calibration file does not exist: nowhere.yml"):
+        camera_from_file(host, "nowhere.yml")
+
+
+def test_generate_remap_maps_matches_opencv(host):
+    """GenerateRemapMaps, camera_params.cc:361-371: Convert<UNDISTORTED, DISTORTED> at every pixel of the undistorted image is the map
+    cv::initUndistortRectifyMap builds for the new camera matrix [f 0 w'/2; 0 f h'/2] (the undistorted frame has its centre at half its
+    size).  Also at scale 0.5."""
+    cv2 = pytest.importorskip("cv2")
+    size = np.array([224, 171], np.int32); us = np.array([260, 200], np.int32)
+    focal = np.array([210.0, 210.0]); center = np.array([112.3, 85.1]); dist = np.array([-0.25, 0.08, 0.0012, -0.0008])
+    K = np.array([[focal[0], 0, center[0]], [0, focal[1], center[1]], [0, 0, 1]])
+    newK = np.array([[focal[0], 0, us[0] / 2.0], [0, focal[1], us[1] / 2.0], [0, 0, 1]])
+    want, _ = cv2.initUndistortRectifyMap(K, dist, np.eye(3), newK, (int(us[0]), int(us[1])), cv2.CV_32FC2)
+    for scale in (1.0, 0.5):
+        buf = np.zeros((int(us[1]), int(us[0]), 2), np.float32)
+        rows, cols = C.c_int(), C.c_int()
+        rc = host.mvh_generate_remap_maps(size.ctypes.data_as(ip), focal.ctypes.data_as(dp), center.ctypes.data_as(dp), dist.ctypes.data_as(dp), 4,
+                                          us.ctypes.data_as(ip), C.c_double(scale), buf.ctypes.data_as(C.POINTER(C.c_float)), C.c_longlong(buf.size // 2),
+                                          C.byref(rows), C.byref(cols))
+        assert rc == 0 and (rows.value, cols.value) == (int(scale * us[1]), int(scale * us[0]))
+        got = buf.ravel()[:2 * rows.value * cols.value].reshape(rows.value, cols.value, 2)
+        step = int(round(1 / scale))
+        assert np.abs(got / scale - want[::step, ::step]).max() < 2e-3
