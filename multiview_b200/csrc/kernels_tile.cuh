@@ -54,6 +54,7 @@ struct TileArgs {
   int icap;                   // residual blocks staged per round
   int nx;                     // max free non-pose columns of one block (focal, centre, distortion, depth)
   int L8max;                  // padded local width the shared buffers are sized for
+  int direct;                 // free non-pose columns go straight from phase b1 into Gt (no Xs staging, one round at a time)
 };
 
 // What phase b1 leaves per residual block.
@@ -71,8 +72,11 @@ __host__ __device__ inline int tile_kk(int K) { int kk = 3 * K; while ((kk & 15)
 // (icap = residual blocks of ONE round; phase b1 evaluates two rounds at a time)
 // Gt[l][3 k + b] = row l of G = F'E of staged track k (dense in the window, zero where the track has no block),
 // Yt = G Hinv in the same layout: phase c is the GEMM  C += Yt Gt'  with the staged tracks as the K dimension.
-__host__ __device__ inline size_t tile_smem(int K, int icap, int nx, int L8max) {
+// direct: no Xs and records of one round only (the free non-pose columns of a block are added to Gt by the thread that evaluates it:
+// with an RPC distortion block floating, Xs was 1.2 KB per residual block and held the round to six tracks)
+__host__ __device__ inline size_t tile_smem(int K, int icap, int nx, int L8max, bool direct = false) {
   const size_t KK = tile_kk(K);
+  if (direct) return (2 * (size_t)L8max * KK + KK + (size_t)K * 6 + (size_t)L8max) * 8 + (size_t)icap * sizeof(TRec) + 16;
   return (2 * (size_t)L8max * KK + KK + (size_t)K * 6 + (size_t)L8max + (size_t)2 * icap * 4 * nx) * 8 + (size_t)2 * icap * sizeof(TRec) + 16;
 }
 
@@ -80,11 +84,15 @@ __host__ __device__ inline size_t tile_smem(int K, int icap, int nx, int L8max) 
 // whole columns once); E carries the landmark scaling.
 // HAS_X = false (no free intrinsics / depth columns anywhere): no distortion Jacobian, no dynamically indexed
 // column loop, so the block's Item stays in registers.
+// Gk != nullptr (direct mode): the free non-pose columns are added to the track's three columns of Gt (Gk = Gt + 3 k, row stride KK)
+// with shared-memory atomics, already Jacobi-scaled (cs); the column loop starts at `rot` so that the blocks of one track, evaluated
+// by neighbouring lanes, are on different rows at any one time.
 template <bool HAS_X>
 __device__ __forceinline__ double tile_eval(const View& v, const BuildArgs& a, const Reduced& S, const TBlk bk, int Wt,
-                                            TRec& rec, double* X, double* jd) {
+                                            TRec& rec, double* X, double* jd, double* Gk = nullptr, const double* cs = nullptr,
+                                            int KK = 0, int rot = 0) {
   Item it;
-  const int kind = bk.kind;
+  const int kind = bk.kind & 0xff;
   const int64_t idx = bk.idx;
   if (kind == 0) eval_cam<true>(v, a.x, a.tab, idx, it, HAS_X ? jd : nullptr, HAS_X ? jd + MVBA_MAXDZ : nullptr);
   else if (kind == 1) eval_depth(v, a.x, a.tab, a.dtab, MVBA_BLOCK_DEPTH_TRI, idx, it);
@@ -133,6 +141,27 @@ __device__ __forceinline__ double tile_eval(const View& v, const BuildArgs& a, c
   if (HAS_X && (sd.c_focal >= 0 || sd.c_center >= 0 || sd.c_dist >= 0 || sd.c_d2i >= 0 || sd.c_scale >= 0)) {
     const int vw = item_vwidth(v, it);
     int n = 0;
+    if (Gk) {
+      const int nv = vw - MVBA_VPOSE;
+      int j = rot % nv;
+      for (int i = 0; i < nv; i++) {
+        const int vc = MVBA_VPOSE + j;
+        if (++j == nv) j = 0;
+        const int gc = item_gcol(v, it, vc);
+        if (gc < 0) continue;
+        double col[3] = {0, 0, 0};
+        item_jcol(v, it, a.tab, a.dtab, vc, jd, jd + MVBA_MAXDZ, col);
+        const int l2 = 7 * Wt + (gc - S.npc);
+        const double sc = sr * cs[l2];
+        double* g = Gk + (size_t)l2 * KK;
+#pragma unroll
+        for (int b = 0; b < 3; b++) {
+          double x = col[0] * Es[b] + col[1] * Es[3 + b];
+          if (it.nr == 3) x += col[2] * Es[6 + b];
+          atomicAdd(g + b, sc * x);
+        }
+      }
+    } else {
     for (int vc = MVBA_VPOSE; vc < vw; vc++) {
       const int gc = item_gcol(v, it, vc);
       if (gc < 0) continue;
@@ -146,6 +175,7 @@ __device__ __forceinline__ double tile_eval(const View& v, const BuildArgs& a, c
       }
       X[4 * n + 3] = (double)(7 * Wt + (gc - S.npc));
       n++;
+    }
     }
     rec.nx = n;
   }
@@ -241,7 +271,7 @@ __global__ void __launch_bounds__(NT, 1) tile_kernel(View v, TileArgs a, Reduced
   double* His = ves + KK;
   double* cs = His + (size_t)K * 6;
   double* Xs = cs + a.L8max;
-  TRec* rec = reinterpret_cast<TRec*>(Xs + (size_t)2 * a.icap * 4 * a.nx);
+  TRec* rec = reinterpret_cast<TRec*>(a.direct ? Xs : Xs + (size_t)2 * a.icap * 4 * a.nx);
   const int B = S.B;
   const int gid = lane >> 2, tig = lane & 3;
   double cost_acc = 0;
@@ -269,11 +299,23 @@ __global__ void __launch_bounds__(NT, 1) tile_kernel(View v, TileArgs a, Reduced
       cs[l] = (a.b.jscale_f && l < Lt) ? a.b.jscale_f[l < 7 * Wt ? 7 * w0 + l : S.npc + (l - 7 * Wt)] : 1.0;
 
     const int rd0 = a.tile_round0[t], rd1 = a.tile_round0[t + 1];
-    for (int rd = rd0; rd < rd1; rd += 2) {
+    const int rstep = a.direct ? 1 : 2;
+    for (int rd = rd0; rd < rd1; rd += rstep) {
       // ---- phase b1 for TWO rounds at once (one thread per residual block, so that most of the CTA evaluates);
-      //      the second round's records sit icap slots further.  Everyone clears Gt. ----
-      const int nsub = min(2, rd1 - rd);
-      {
+      //      the second round's records sit icap slots further.  Everyone clears Gt.
+      //      Direct mode: ONE round; Gt is cleared first, then every block adds its free non-pose columns to it. ----
+      const int nsub = min(rstep, rd1 - rd);
+      if (a.direct) {
+        double2* gz = reinterpret_cast<double2*>(Gt);
+        const int nz = L8 * KK / 2;
+        for (int i = tid; i < nz; i += NT) gz[i] = make_double2(0.0, 0.0);
+        __syncthreads();   // also orders cs (written at the start of the tile) before its first reader
+        const int blk0 = a.round_blk0[rd], nit = a.round_blk0[rd + 1] - blk0;
+        for (int q = tid; q < nit; q += NT) {
+          const TBlk bk = a.blk[blk0 + q];
+          cost_acc += tile_eval<true>(v, a.b, S, bk, Wt, rec[q], nullptr, jd, Gt + 3 * ((bk.kind >> 8) & 0xff), cs, KK, 5 * q);
+        }
+      } else {
         const int blk0 = a.round_blk0[rd], nit0 = a.round_blk0[rd + 1] - blk0, nit = a.round_blk0[rd + nsub] - blk0;
         if (a.nx > 0) {
           for (int q = tid; q < nit; q += NT) {
@@ -287,7 +329,7 @@ __global__ void __launch_bounds__(NT, 1) tile_kernel(View v, TileArgs a, Reduced
           }
         }
       }
-      {
+      if (!a.direct) {
         double2* gz = reinterpret_cast<double2*>(Gt);
         const int nz = L8 * KK / 2;
         for (int i = tid; i < nz; i += NT) gz[i] = make_double2(0.0, 0.0);
@@ -341,7 +383,7 @@ __global__ void __launch_bounds__(NT, 1) tile_kernel(View v, TileArgs a, Reduced
         ves[3 * tid + 1] = Hi[1] * gE[0] + Hi[3] * gE[1] + Hi[4] * gE[2];
         ves[3 * tid + 2] = Hi[2] * gE[0] + Hi[4] * gE[1] + Hi[5] * gE[2];
       }
-      if (a.nx > 0) {  // free intrinsics / depth columns staged by phase b1: a warp per track, disjoint from the gathered columns
+      if (a.nx > 0 && !a.direct) {  // free intrinsics / depth columns staged by phase b1: a warp per track, disjoint from the gathered columns
         for (int k = wib; k < kc; k += NW) {
           const TTrk tk = a.ttrk[trk0 + k];
           double* G = Gt + 3 * k;

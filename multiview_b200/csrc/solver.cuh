@@ -134,7 +134,7 @@ struct Solver {
   // (static round tables: staged blocks, per-track slots, gather groups and their contributors, kernels_tile.cuh)
   DBuf<int32_t> tile_w0, tile_wn, tile_round0, round_trk0, round_blk0, round_grp0, fallback;
   DBuf<TBlk> t_blk; DBuf<TTrk> t_trk; DBuf<TGrp> t_grp; DBuf<uint16_t> t_con;
-  int ntiles = 0, nrounds = 0, nfallback = 0, tile_nt = 512, tile_pr = 4, tile_K = 1, tile_icap = 64, tile_nx = 0, tile_L8max = 8, grid_tile = 1;
+  int ntiles = 0, nrounds = 0, nfallback = 0, tile_nt = 512, tile_pr = 4, tile_K = 1, tile_icap = 64, tile_nx = 0, tile_L8max = 8, grid_tile = 1, tile_direct = 0;
   size_t smem_tile = 0;
   // pass B, staged variant (kernels_tile2.cuh): per-round blobs fetched by bulk copy, two CTAs per SM
   bool any_x = false, tile2 = false;
@@ -465,18 +465,24 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
       }
     }
     s->tile2 = use_t2;
+    s->tile_direct = 0;
     if (use_t2) { s->tile_K = s->t2_K; s->tile_icap = s->t2_icap; }
     else {
       // the largest K (tracks per round) whose staging fits, with room for ~1.15 x the mean number of blocks per track
+      // wide free blocks (an RPC distortion block: 38 columns, 1.2 KB of staging per residual block) go from the evaluating thread
+      // straight into the round's G (shared-memory atomics) instead of through a staging buffer that would hold the round to a few tracks
+      bool direct = nx >= 16;
+      if (const char* ev = std::getenv("MVBA_TILE_DIRECT")) direct = nx > 0 && ev[0] == '1';   // developer switch
+      s->tile_direct = direct;
       int K = 32, icap = 0;  // phase b3 maps the staged tracks to the lanes of a warp
       for (; K >= 1; K--) {
         icap = (int)std::min<double>(511.0, std::max(32.0, std::ceil(1.15 * mean_items * K)));
-        if (tile_smem(K, icap, nx, s->tile_L8max) + 1024 <= (size_t)dev_smem) break;
+        if (tile_smem(K, icap, nx, s->tile_L8max, direct) + 1024 <= (size_t)dev_smem) break;
       }
       if (K < 1) return fail(MVBA_EINVAL, "mvba: tile staging does not fit shared memory");
-      while (icap < 511 && tile_smem(K, icap + 1, nx, s->tile_L8max) + 1024 <= (size_t)dev_smem && icap < 2 * mean_items * K) icap++;
+      while (icap < 511 && tile_smem(K, icap + 1, nx, s->tile_L8max, direct) + 1024 <= (size_t)dev_smem && icap < 2 * mean_items * K) icap++;
       s->tile_K = K; s->tile_icap = icap;
-      s->smem_tile = tile_smem(s->tile_K, s->tile_icap, nx, s->tile_L8max);
+      s->smem_tile = tile_smem(s->tile_K, s->tile_icap, nx, s->tile_L8max, direct);
       // accumulator blocks per warp: upper block triangle of the widest window over 16 warps
       const int nb8 = s->tile_L8max / 8, per = (nb8 * (nb8 + 1) / 2 + 15) / 16;
       s->tile_pr = per <= 4 ? 4 : per <= 8 ? 8 : 16;
@@ -549,9 +555,10 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
             if (sd.c_rig >= 0) contribute(7 * Wt + (sd.c_rig - s->npc), 0, slot, 2);
             if (sd.c_off >= 0) contribute(7 * Wt + (sd.c_off - s->npc), 1, slot, 3);
           };
-          for (int64_t i = h->h_trk_obs0[p]; i < h->h_trk_obs0[p + 1]; i++) { blk.push_back(TBlk{(int32_t)i, 0}); f_block(i, q++); }
-          for (int64_t j = h->h_trk_dtri0[p]; j < h->h_trk_dtri0[p + 1]; j++) { blk.push_back(TBlk{(int32_t)j, 1}); f_block(h->h_dtri_obs[j], q++); }
-          for (int64_t j = h->h_trk_dmesh0[p]; j < h->h_trk_dmesh0[p + 1]; j++) { blk.push_back(TBlk{(int32_t)j, 2}); f_block(h->h_dmesh_obs[j], q++); }
+          const int kslot = s->tile_direct ? (k << 8) : 0;   // direct mode: the evaluating thread needs the track's position in the round
+          for (int64_t i = h->h_trk_obs0[p]; i < h->h_trk_obs0[p + 1]; i++) { blk.push_back(TBlk{(int32_t)i, 0 | kslot}); f_block(i, q++); }
+          for (int64_t j = h->h_trk_dtri0[p]; j < h->h_trk_dtri0[p + 1]; j++) { blk.push_back(TBlk{(int32_t)j, 1 | kslot}); f_block(h->h_dtri_obs[j], q++); }
+          for (int64_t j = h->h_trk_dmesh0[p]; j < h->h_trk_dmesh0[p + 1]; j++) { blk.push_back(TBlk{(int32_t)j, 2 | kslot}); f_block(h->h_dmesh_obs[j], q++); }
           for (int64_t j = h->h_trk_pm0[p]; j < h->h_trk_pm0[p + 1]; j++) { blk.push_back(TBlk{(int32_t)j, 3}); q++; }
           for (int64_t j = h->h_trk_pt0[p]; j < h->h_trk_pt0[p + 1]; j++) { blk.push_back(TBlk{(int32_t)j, 4}); q++; }
           for (const Key& key : keys) {

@@ -232,6 +232,8 @@ def test_mesh_and_depth_flags(dataset, oracle_lib):
     d, _ = dataset
     pr = synth.make_problem(seed=31, sensors="rig3", num_ref=10, num_landmarks=120, obs_per_track=5)
     names = [s.name for s in pr.sensors]
+    # the fixture's rig_config.txt carries the identity as depth_to_image_transform for every sensor: the oracle's problem must too
+    pr.depth_to_image[:] = np.tile([0, 0, 0, 0, 0, 0, 1.0], len(pr.sensors)); pr.depth_scale[:] = 1.0
     has, dxyz, verts, faces = depth_and_mesh_inputs(d, pr)
     out = run(d, "--bracket_len", "1.0", "--calibrator_num_passes", "1", "--num_iterations", "4", "--use_initial_rig_transforms",
               "--camera_poses_to_float", names[0], "--rig_transforms_to_float", " ".join(names[1:]), "--mesh", str(d / "box.ply"),
