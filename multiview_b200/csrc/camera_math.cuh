@@ -185,6 +185,16 @@ __device__ inline void prep_depth(const View& v, const double* __restrict__ x, i
   }
 }
 
+// Packed order of the RPC coefficients (rpc_distortion.cc:116-160): numerator of x (all monomials up to `deg`, degree-major,
+// inside a degree by the power of y), denominator of x (the same without the constant term, which is 1), numerator of y,
+// denominator of y.  rpc_tri(d) + i is the place of ux^(d-i) uy^i in a numerator block; a denominator block is one shorter.
+struct RpcLayout { int o1, o2, o3, n; };   // first entry of den_x, num_y, den_y; number of coefficients of one half
+__host__ __device__ __forceinline__ int rpc_tri(int d) { return d * (d + 1) / 2; }
+__host__ __device__ __forceinline__ RpcLayout rpc_layout(int deg) {
+  const int nn = (deg + 1) * (deg + 2) / 2;
+  return RpcLayout{nn, 2 * nn - 1, 3 * nn - 1, 4 * nn - 2};
+}
+
 // One BracketedCamError evaluation (rig_calibrator.cc:447-482) given Xc = world_to_cam * X.
 //   r = Convert<UNDISTORTED_C,DISTORTED>(f * Xc.xy / Xc.z) - meas
 // Outputs: r[2]; A = dr/dXc (2x3 row-major); Jf = dr/dfocal (2); Jc: dr/dcenter = Jc * I2;
@@ -262,49 +272,55 @@ __device__ __forceinline__ void project_distort(const SensorDev& s, const double
     // normalisation and no optical-centre term.
     const int deg = s.rpc_deg;
     const double ux = f * px, uy = f * py;
-    double powx[8], powy[8];
-    powx[0] = 1; powy[0] = 1;
-    for (int d = 1; d <= deg; d++) { powx[d] = powx[d - 1] * ux; powy[d] = powy[d - 1] * uy; }
-    double val[4] = {0, 1, 0, 1}, vx[4] = {0, 0, 0, 0}, vy[4] = {0, 0, 0, 0};
-    int ci = 0;
-    for (int cnt = 0; cnt < 4; cnt++) {
-      for (int d = (cnt & 1); d <= deg; d++) {
-        for (int i = 0; i <= d; i++, ci++) {
-          double co = dist[ci];
-          int a = d - i;
-          val[cnt] += co * powx[a] * powy[i];
+    // The monomials ux^a uy^i are walked i-major with running products (no power tables: a dynamically indexed local array
+    // would live in local memory); rpc_ci gives the coefficient's place in the reference's packed order.
+    const RpcLayout L = rpc_layout(deg);
+    double v0 = 0, v1 = 1, v2 = 0, v3 = 1, x0 = 0, x1 = 0, x2 = 0, x3 = 0, y0 = 0, y1 = 0, y2 = 0, y3 = 0;
+    {
+      double yi = 1.0, yi1 = 0.0;  // uy^i, uy^(i-1)
+      for (int i = 0; i <= deg; i++) {
+        double m = yi, mx = 0.0, my = yi1;  // ux^a uy^i, ux^(a-1) uy^i, ux^a uy^(i-1)
+        for (int a = 0; a + i <= deg; a++) {
+          const int o = rpc_tri(a + i) + i;
+          const double c0 = dist[o], c2 = dist[L.o2 + o];
+          const double c1 = (a + i > 0) ? dist[L.o1 + o - 1] : 0.0, c3 = (a + i > 0) ? dist[L.o3 + o - 1] : 0.0;
+          v0 = fma(c0, m, v0); v1 = fma(c1, m, v1); v2 = fma(c2, m, v2); v3 = fma(c3, m, v3);
           if (WANT_J) {
-            if (a > 0) vx[cnt] += co * a * powx[a - 1] * powy[i];
-            if (i > 0) vy[cnt] += co * i * powx[a] * powy[i - 1];
+            const double dxm = a * mx, dym = i * my;
+            x0 = fma(c0, dxm, x0); x1 = fma(c1, dxm, x1); x2 = fma(c2, dxm, x2); x3 = fma(c3, dxm, x3);
+            y0 = fma(c0, dym, y0); y1 = fma(c1, dym, y1); y2 = fma(c2, dym, y2); y3 = fma(c3, dym, y3);
           }
+          mx = m; m *= ux; my *= ux;
         }
+        yi1 = yi; yi *= uy;
       }
     }
-    const double idx = 1.0 / val[1], idy = 1.0 / val[3];
-    const double ox = val[0] * idx, oy = val[2] * idy;
+    const double idx = 1.0 / v1, idy = 1.0 / v3;
+    const double ox = v0 * idx, oy = v2 * idy;
     dx = ox + hx; dy = oy + hy;
     if (WANT_J) {
       // d(out)/d(u) then u = f p
-      double dox_dux = (vx[0] - ox * vx[1]) * idx, dox_duy = (vy[0] - ox * vy[1]) * idx;
-      double doy_dux = (vx[2] - oy * vx[3]) * idy, doy_duy = (vy[2] - oy * vy[3]) * idy;
+      double dox_dux = (x0 - ox * x1) * idx, dox_duy = (y0 - ox * y1) * idx;
+      double doy_dux = (x2 - oy * x3) * idy, doy_duy = (y2 - oy * y3) * idy;
       dpx[0] = f * dox_dux; dpx[1] = f * doy_dux;
       dpy[0] = f * dox_duy; dpy[1] = f * doy_duy;
       Jf[0] = dox_dux * px + dox_duy * py; Jf[1] = doy_dux * px + doy_duy * py;
       *Jc = 0.0;
       if (Jd0) {
-        ci = 0;
-        for (int cnt = 0; cnt < 4; cnt++) {
-          for (int d = (cnt & 1); d <= deg; d++) {
-            for (int i = 0; i <= d; i++, ci++) {
-              double mono = powx[d - i] * powy[i];
-              double a0 = 0, a1 = 0;
-              if (cnt == 0) a0 = mono * idx;
-              else if (cnt == 1) a0 = -ox * mono * idx;
-              else if (cnt == 2) a1 = mono * idy;
-              else a1 = -oy * mono * idy;
-              Jd0[ci] = a0; Jd1[ci] = a1;
+        double yi = 1.0;
+        for (int i = 0; i <= deg; i++) {
+          double m = yi;
+          for (int a = 0; a + i <= deg; a++) {
+            const int o = rpc_tri(a + i) + i;
+            Jd0[o] = m * idx; Jd1[o] = 0.0;
+            Jd0[L.o2 + o] = 0.0; Jd1[L.o2 + o] = m * idy;
+            if (a + i > 0) {
+              Jd0[L.o1 + o - 1] = -ox * m * idx; Jd1[L.o1 + o - 1] = 0.0;
+              Jd0[L.o3 + o - 1] = 0.0; Jd1[L.o3 + o - 1] = -oy * m * idy;
             }
+            m *= ux;
           }
+          yi *= uy;
         }
       }
     }

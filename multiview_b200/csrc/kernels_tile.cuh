@@ -94,7 +94,10 @@ __device__ __forceinline__ double tile_eval(const View& v, const BuildArgs& a, c
   Item it;
   const int kind = bk.kind & 0xff;
   const int64_t idx = bk.idx;
-  if (kind == 0) eval_cam<true>(v, a.x, a.tab, idx, it, HAS_X ? jd : nullptr, HAS_X ? jd + MVBA_MAXDZ : nullptr);
+  // direct mode, RPC sensor: the 38+ distortion columns are formed on the fly below, no dr/d(distortion) table (1 KB of local memory
+  // per thread, which the 29 KB of L1 left beside this kernel's shared memory cannot hold)
+  const bool rpc_fly = HAS_X && Gk != nullptr && kind == 0 && v.sens[v.cam_sensor[v.cid[idx]]].rpc_deg > 0;
+  if (kind == 0) eval_cam<true>(v, a.x, a.tab, idx, it, HAS_X && !rpc_fly ? jd : nullptr, HAS_X && !rpc_fly ? jd + MVBA_MAXDZ : nullptr);
   else if (kind == 1) eval_depth(v, a.x, a.tab, a.dtab, MVBA_BLOCK_DEPTH_TRI, idx, it);
   else if (kind == 2) eval_depth(v, a.x, a.tab, a.dtab, MVBA_BLOCK_DEPTH_MESH, idx, it);
   else eval_prior(v, a.x, idx, it);
@@ -141,7 +144,60 @@ __device__ __forceinline__ double tile_eval(const View& v, const BuildArgs& a, c
   if (HAS_X && (sd.c_focal >= 0 || sd.c_center >= 0 || sd.c_dist >= 0 || sd.c_d2i >= 0 || sd.c_scale >= 0)) {
     const int vw = item_vwidth(v, it);
     int n = 0;
-    if (Gk) {
+    if (rpc_fly) {
+      // one column of this block's F'E, scaled, into the track's G: j0, j1 = the column's entries in the two residual rows
+      auto add_col = [&](int gc, double j0, double j1) {
+        const int l2 = 7 * Wt + (gc - S.npc);
+        const double sc = sr * cs[l2];
+        double* g = Gk + (size_t)l2 * KK;
+        atomicAdd(g, sc * (j0 * Es[0] + j1 * Es[3]));
+        atomicAdd(g + 1, sc * (j0 * Es[1] + j1 * Es[4]));
+        atomicAdd(g + 2, sc * (j0 * Es[2] + j1 * Es[5]));
+      };
+      if (sd.c_focal >= 0) add_col(sd.c_focal, it.Jf[0], it.Jf[1]);
+      // dr/d(centre) = Jc I with Jc = 0 for the RPC model: those columns get nothing from this block
+      if (sd.c_dist >= 0) {
+        const double* dist = a.x + sd.x_dist;
+        const int deg = sd.rpc_deg;
+        const RpcLayout L = rpc_layout(deg);
+        const double fz = a.x[sd.x_focal] / it.Xc[2];
+        const double ux = fz * it.Xc[0], uy = fz * it.Xc[1];
+        double v0 = 0, v1 = 1, v2 = 0, v3 = 1;
+        {
+          double yi = 1.0;
+          for (int i = 0; i <= deg; i++) {
+            double m = yi;
+            for (int aa = 0; aa + i <= deg; aa++) {
+              const int o = rpc_tri(aa + i) + i;
+              v0 = fma(dist[o], m, v0); v2 = fma(dist[L.o2 + o], m, v2);
+              if (aa + i > 0) { v1 = fma(dist[L.o1 + o - 1], m, v1); v3 = fma(dist[L.o3 + o - 1], m, v3); }
+              m *= ux;
+            }
+            yi *= uy;
+          }
+        }
+        const double idx2 = 1.0 / v1, idy2 = 1.0 / v3;
+        const double nox = -(v0 * idx2) * idx2, noy = -(v2 * idy2) * idy2;   // -ox / den_x, -oy / den_y
+        // the blocks of one track sit in neighbouring lanes: each starts at a different power of y, so that they are
+        // on different rows of G most of the time
+        int i = rot % (deg + 1);
+        for (int ii = 0; ii <= deg; ii++) {
+          double m = 1.0;
+          for (int e = 0; e < i; e++) m *= uy;
+          for (int aa = 0; aa + i <= deg; aa++) {
+            const int o = rpc_tri(aa + i) + i;
+            add_col(sd.c_dist + o, m * idx2, 0.0);
+            add_col(sd.c_dist + L.o2 + o, 0.0, m * idy2);
+            if (aa + i > 0) {
+              add_col(sd.c_dist + L.o1 + o - 1, m * nox, 0.0);
+              add_col(sd.c_dist + L.o3 + o - 1, 0.0, m * noy);
+            }
+            m *= ux;
+          }
+          if (++i > deg) i = 0;
+        }
+      }
+    } else if (Gk) {
       const int nv = vw - MVBA_VPOSE;
       int j = rot % nv;
       for (int i = 0; i < nv; i++) {
