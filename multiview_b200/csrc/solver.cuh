@@ -382,7 +382,8 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
       for (int p = 0; p < v.P; p++) if (trk_any[p]) { any++; wide += (trk_span[p] > capw2 || trk_items[p] > 32); }
       if (s->B > 119 || capw2 < 1 || wide * 100 > any) use_t2 = false;
     }
-    const int capw = use_t2 ? capw2 : (176 - s->B) / 7;
+    int capw = use_t2 ? capw2 : (176 - s->B) / 7;
+    if (const char* ev = std::getenv("MVBA_TILE_WCAP")) { const int w = std::atoi(ev); if (!use_t2 && w >= 1) capw = std::min(capw, w); }  // developer switch
     int W = std::min(maxspan + 2, capw);
     if (s->B > 176 || W < 0) W = -1;  // nothing fits: every track takes the generic kernel
     std::vector<int32_t> order, fb;
@@ -485,9 +486,10 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
       s->smem_tile = tile_smem(s->tile_K, s->tile_icap, nx, s->tile_L8max, direct);
       // accumulator blocks per warp: upper block triangle of the widest window over 16 warps
       const int nb8 = s->tile_L8max / 8, per = (nb8 * (nb8 + 1) / 2 + 15) / 16;
-      s->tile_pr = per <= 4 ? 4 : per <= 8 ? 8 : 16;
+      s->tile_pr = per <= 4 ? 4 : per <= 8 ? 8 : per <= 12 ? 12 : 16;
       if (s->tile_pr == 4) MVBA_CUDA(cudaFuncSetAttribute(tile_kernel<512, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_tile));
       else if (s->tile_pr == 8) MVBA_CUDA(cudaFuncSetAttribute(tile_kernel<512, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_tile));
+      else if (s->tile_pr == 12) MVBA_CUDA(cudaFuncSetAttribute(tile_kernel<512, 12>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_tile));
       else MVBA_CUDA(cudaFuncSetAttribute(tile_kernel<512, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_tile));
     }
     const int gcap = use_t2 ? MVBA_T2_GCAP : INT32_MAX;  // gather groups of one round
