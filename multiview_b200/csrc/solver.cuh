@@ -486,14 +486,15 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
       s->smem_tile = tile_smem(s->tile_K, s->tile_icap, nx, s->tile_L8max, direct);
       // accumulator blocks per warp: upper block triangle of the widest window over 16 warps.  Beyond 8 per warp the 512-thread
       // kernel (128 registers per thread) keeps part of its accumulators in local memory and every DMMA of those slots is a
-      // load / store round trip: such windows run on 256 threads (255 registers) with up to 24 blocks per warp when that covers them
+      // load / store round trip: such windows run on 256 threads (255 registers) with 24 or 32 blocks per warp
       const int nb8 = s->tile_L8max / 8, nblk = nb8 * (nb8 + 1) / 2, per = (nblk + 15) / 16, per8 = (nblk + 7) / 8;
       s->tile_nt = 512;
       s->tile_pr = per <= 4 ? 4 : per <= 8 ? 8 : per <= 12 ? 12 : 16;
-      bool wide256 = per > 8 && per8 <= 24;
+      bool wide256 = per > 8 && per8 <= 32;
       if (const char* ev = std::getenv("MVBA_TILE_256")) wide256 = wide256 && ev[0] != '0';   // developer switch
-      if (wide256) { s->tile_nt = 256; s->tile_pr = 24; }
-      if (s->tile_nt == 256) MVBA_CUDA(cudaFuncSetAttribute(tile_kernel<256, 24>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_tile));
+      if (wide256) { s->tile_nt = 256; s->tile_pr = per8 <= 24 ? 24 : 32; }
+      if (s->tile_nt == 256 && s->tile_pr == 24) MVBA_CUDA(cudaFuncSetAttribute(tile_kernel<256, 24>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_tile));
+      else if (s->tile_nt == 256) MVBA_CUDA(cudaFuncSetAttribute(tile_kernel<256, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_tile));
       else if (s->tile_pr == 4) MVBA_CUDA(cudaFuncSetAttribute(tile_kernel<512, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_tile));
       else if (s->tile_pr == 8) MVBA_CUDA(cudaFuncSetAttribute(tile_kernel<512, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_tile));
       else if (s->tile_pr == 12) MVBA_CUDA(cudaFuncSetAttribute(tile_kernel<512, 12>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s->smem_tile));
