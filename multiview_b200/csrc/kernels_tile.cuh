@@ -55,7 +55,9 @@ struct TileArgs {
   int nx;                     // max free non-pose columns of one block (focal, centre, distortion, depth)
   int L8max;                  // padded local width the shared buffers are sized for
   int direct;                 // free non-pose columns go straight from phase b1 into Gt (no Xs staging, one round at a time)
+  int nmono;                  // direct mode: monomials of the widest floating RPC model (0: none); phase b2 forms those columns
 };
+#define MVBA_XR 14            // per-block RPC record of direct mode: ux uy 1/den_x 1/den_y -ox/den_x -oy/den_y  sr Es[0..5]  Jf[0..1]
 
 // What phase b1 leaves per residual block.
 struct TRec {
@@ -76,7 +78,7 @@ __host__ __device__ inline int tile_kk(int K) { int kk = 3 * K; while ((kk & 15)
 // with an RPC distortion block floating, Xs was 1.2 KB per residual block and held the round to six tracks)
 __host__ __device__ inline size_t tile_smem(int K, int icap, int nx, int L8max, bool direct = false) {
   const size_t KK = tile_kk(K);
-  if (direct) return (2 * (size_t)L8max * KK + KK + (size_t)K * 6 + (size_t)L8max) * 8 + (size_t)icap * sizeof(TRec) + 16;
+  if (direct) return (2 * (size_t)L8max * KK + KK + (size_t)K * 6 + (size_t)L8max + (size_t)icap * MVBA_XR) * 8 + (size_t)icap * sizeof(TRec) + 16;
   return (2 * (size_t)L8max * KK + KK + (size_t)K * 6 + (size_t)L8max + (size_t)2 * icap * 4 * nx) * 8 + (size_t)2 * icap * sizeof(TRec) + 16;
 }
 
@@ -90,7 +92,7 @@ __host__ __device__ inline size_t tile_smem(int K, int icap, int nx, int L8max, 
 template <bool HAS_X>
 __device__ __forceinline__ double tile_eval(const View& v, const BuildArgs& a, const Reduced& S, const TBlk bk, int Wt,
                                             TRec& rec, double* X, double* jd, double* Gk = nullptr, const double* cs = nullptr,
-                                            int KK = 0, int rot = 0) {
+                                            int KK = 0, int rot = 0, double* xr = nullptr) {
   Item it;
   const int kind = bk.kind & 0xff;
   const int64_t idx = bk.idx;
@@ -145,58 +147,35 @@ __device__ __forceinline__ double tile_eval(const View& v, const BuildArgs& a, c
     const int vw = item_vwidth(v, it);
     int n = 0;
     if (rpc_fly) {
-      // one column of this block's F'E, scaled, into the track's G: j0, j1 = the column's entries in the two residual rows
-      auto add_col = [&](int gc, double j0, double j1) {
-        const int l2 = 7 * Wt + (gc - S.npc);
-        const double sc = sr * cs[l2];
-        double* g = Gk + (size_t)l2 * KK;
-        atomicAdd(g, sc * (j0 * Es[0] + j1 * Es[3]));
-        atomicAdd(g + 1, sc * (j0 * Es[1] + j1 * Es[4]));
-        atomicAdd(g + 2, sc * (j0 * Es[2] + j1 * Es[5]));
-      };
-      if (sd.c_focal >= 0) add_col(sd.c_focal, it.Jf[0], it.Jf[1]);
-      // dr/d(centre) = Jc I with Jc = 0 for the RPC model: those columns get nothing from this block
-      if (sd.c_dist >= 0) {
-        const double* dist = a.x + sd.x_dist;
-        const int deg = sd.rpc_deg;
-        const RpcLayout L = rpc_layout(deg);
-        const double fz = a.x[sd.x_focal] / it.Xc[2];
-        const double ux = fz * it.Xc[0], uy = fz * it.Xc[1];
-        double v0 = 0, v1 = 1, v2 = 0, v3 = 1;
-        {
-          double yi = 1.0;
-          for (int i = 0; i <= deg; i++) {
-            double m = yi;
-            for (int aa = 0; aa + i <= deg; aa++) {
-              const int o = rpc_tri(aa + i) + i;
-              v0 = fma(dist[o], m, v0); v2 = fma(dist[L.o2 + o], m, v2);
-              if (aa + i > 0) { v1 = fma(dist[L.o1 + o - 1], m, v1); v3 = fma(dist[L.o3 + o - 1], m, v3); }
-              m *= ux;
-            }
-            yi *= uy;
-          }
-        }
-        const double idx2 = 1.0 / v1, idy2 = 1.0 / v3;
-        const double nox = -(v0 * idx2) * idx2, noy = -(v2 * idy2) * idy2;   // -ox / den_x, -oy / den_y
-        // the blocks of one track sit in neighbouring lanes: each starts at a different power of y, so that they are
-        // on different rows of G most of the time
-        int i = rot % (deg + 1);
-        for (int ii = 0; ii <= deg; ii++) {
-          double m = 1.0;
-          for (int e = 0; e < i; e++) m *= uy;
+      // RPC sensor, direct mode: no column is formed here.  The block leaves the few numbers its focal and distortion columns are
+      // made of (MVBA_XR doubles); phase b2 has one thread per (track, monomial) sum them over the track's blocks and store the
+      // rows of G it alone owns -- no staging of 38 columns per block and no shared-memory atomics (a CAS loop each).
+      const double* dist = a.x + sd.x_dist;
+      const int deg = sd.rpc_deg;
+      const RpcLayout L = rpc_layout(deg);
+      const double fz = a.x[sd.x_focal] / it.Xc[2];
+      const double ux = fz * it.Xc[0], uy = fz * it.Xc[1];
+      double v0 = 0, v1 = 1, v2 = 0, v3 = 1;
+      {
+        double yi = 1.0;
+        for (int i = 0; i <= deg; i++) {
+          double m = yi;
           for (int aa = 0; aa + i <= deg; aa++) {
             const int o = rpc_tri(aa + i) + i;
-            add_col(sd.c_dist + o, m * idx2, 0.0);
-            add_col(sd.c_dist + L.o2 + o, 0.0, m * idy2);
-            if (aa + i > 0) {
-              add_col(sd.c_dist + L.o1 + o - 1, m * nox, 0.0);
-              add_col(sd.c_dist + L.o3 + o - 1, 0.0, m * noy);
-            }
+            v0 = fma(dist[o], m, v0); v2 = fma(dist[L.o2 + o], m, v2);
+            if (aa + i > 0) { v1 = fma(dist[L.o1 + o - 1], m, v1); v3 = fma(dist[L.o3 + o - 1], m, v3); }
             m *= ux;
           }
-          if (++i > deg) i = 0;
+          yi *= uy;
         }
       }
+      const double idx2 = 1.0 / v1, idy2 = 1.0 / v3;
+      xr[0] = ux; xr[1] = uy; xr[2] = idx2; xr[3] = idy2;
+      xr[4] = -(v0 * idx2) * idx2; xr[5] = -(v2 * idy2) * idy2;   // -ox / den_x, -oy / den_y
+#pragma unroll
+      for (int b = 0; b < 6; b++) xr[6 + b] = sr * Es[b];
+      xr[12] = it.Jf[0]; xr[13] = it.Jf[1];
+      n = -1;   // marks the record for phase b2
     } else if (Gk) {
       const int nv = vw - MVBA_VPOSE;
       int j = rot % nv;
@@ -327,7 +306,7 @@ __global__ void __launch_bounds__(NT, 1) tile_kernel(View v, TileArgs a, Reduced
   double* His = ves + KK;
   double* cs = His + (size_t)K * 6;
   double* Xs = cs + a.L8max;
-  TRec* rec = reinterpret_cast<TRec*>(a.direct ? Xs : Xs + (size_t)2 * a.icap * 4 * a.nx);
+  TRec* rec = reinterpret_cast<TRec*>(a.direct ? Xs + (size_t)a.icap * MVBA_XR : Xs + (size_t)2 * a.icap * 4 * a.nx);
   const int B = S.B;
   const int gid = lane >> 2, tig = lane & 3;
   double cost_acc = 0;
@@ -350,6 +329,13 @@ __global__ void __launch_bounds__(NT, 1) tile_kernel(View v, TileArgs a, Reduced
 #pragma unroll
     for (int i = 0; i < MAXS; i++) { acc[i][0] = 0; acc[i][1] = 0; }
     double rhs_acc = 0;
+    unsigned rowend = 0;               // wide windows: the slots after which the block row changes
+    if constexpr (MAXS >= 24) {
+      int bi = bi0, bj = bj0;
+#pragma unroll
+      for (int sl = 0; sl < MAXS; sl++)
+        if (sl < ns && ++bj == nb8) { bi++; bj = bi; rowend |= 1u << sl; }
+    }
     // Jacobi scale of every local column (the previous tile's readers are behind its last barrier)
     for (int l = tid; l < a.L8max; l += NT)
       cs[l] = (a.b.jscale_f && l < Lt) ? a.b.jscale_f[l < 7 * Wt ? 7 * w0 + l : S.npc + (l - 7 * Wt)] : 1.0;
@@ -369,7 +355,8 @@ __global__ void __launch_bounds__(NT, 1) tile_kernel(View v, TileArgs a, Reduced
         const int blk0 = a.round_blk0[rd], nit = a.round_blk0[rd + 1] - blk0;
         for (int q = tid; q < nit; q += NT) {
           const TBlk bk = a.blk[blk0 + q];
-          cost_acc += tile_eval<true>(v, a.b, S, bk, Wt, rec[q], nullptr, jd, Gt + 3 * ((bk.kind >> 8) & 0xff), cs, KK, 5 * q);
+          cost_acc += tile_eval<true>(v, a.b, S, bk, Wt, rec[q], nullptr, jd, Gt + 3 * ((bk.kind >> 8) & 0xff), cs, KK, 5 * q,
+                                      Xs + (size_t)q * MVBA_XR);
         }
       } else {
         const int blk0 = a.round_blk0[rd], nit0 = a.round_blk0[rd + 1] - blk0, nit = a.round_blk0[rd + nsub] - blk0;
@@ -414,6 +401,59 @@ __global__ void __launch_bounds__(NT, 1) tile_kernel(View v, TileArgs a, Reduced
           const int4 rawn = inext < 8 * ngrp ? __ldg(gtab + (inext >> 3)) : make_int4(0, 0, 0, 0);
           tile_gather(a, raw, i & 7, rec_s, cs, Gt, KK);
           raw = rawn; i = inext;
+        }
+      }
+      if (a.direct && a.nmono > 0) {
+        // focal and RPC distortion rows of G: one thread per (track, monomial | focal) sums over the track's RPC blocks from their
+        // MVBA_XR records and adds to rows of Gt that no other thread touches (runs of blocks of one sensor are summed in registers)
+        const int per = a.nmono + 1, ntask = kc * per;
+        for (int t = tid; t < ntask; t += NT) {
+          const int k = t / per, mi = t - k * per;
+          const TTrk tk = a.ttrk[trk0 + k];
+          double* G = Gt + 3 * k;
+          int d = 0;
+          while (rpc_tri(d + 1) <= mi) d++;
+          const int iy = mi - rpc_tri(d), ax = d - iy;
+          const bool focal = mi == a.nmono;
+          int cur = -1;
+          double s0[3] = {0, 0, 0}, s1[3] = {0, 0, 0}, s2[3] = {0, 0, 0}, s3[3] = {0, 0, 0};
+          auto flush = [&](int sensor) {
+            const SensorDev& sd = v.sens[sensor];
+            auto put = [&](int gc, const double* sv) {
+              const int l2 = 7 * Wt + (gc - S.npc);
+              const double sc = cs[l2];
+              double* g = G + (size_t)l2 * KK;
+              g[0] += sv[0] * sc; g[1] += sv[1] * sc; g[2] += sv[2] * sc;
+            };
+            if (focal) { if (sd.c_focal >= 0) put(sd.c_focal, s0); }
+            else if (sd.c_dist >= 0 && d <= sd.rpc_deg) {
+              const RpcLayout L = rpc_layout(sd.rpc_deg);
+              put(sd.c_dist + mi, s0);
+              put(sd.c_dist + L.o2 + mi, s2);
+              if (d > 0) { put(sd.c_dist + L.o1 + mi - 1, s1); put(sd.c_dist + L.o3 + mi - 1, s3); }
+            }
+#pragma unroll
+            for (int b = 0; b < 3; b++) { s0[b] = 0; s1[b] = 0; s2[b] = 0; s3[b] = 0; }
+          };
+          for (int i = 0; i < tk.n; i++) {
+            const TRec& r = rec_s[tk.q0 + i];
+            if (r.nx != -1) continue;
+            const int sensor = v.cam_sensor[r.cid];
+            if (sensor != cur) { if (cur >= 0) flush(cur); cur = sensor; }
+            const double* x = Xs + (size_t)(tk.q0 + i) * MVBA_XR;
+            if (focal) {
+#pragma unroll
+              for (int b = 0; b < 3; b++) s0[b] += x[12] * x[6 + b] + x[13] * x[9 + b];
+            } else {
+              double m = 1.0;
+              for (int e = 0; e < ax; e++) m *= x[0];
+              for (int e = 0; e < iy; e++) m *= x[1];
+              const double a0 = m * x[2], a1 = m * x[4], a2 = m * x[3], a3 = m * x[5];
+#pragma unroll
+              for (int b = 0; b < 3; b++) { s0[b] += a0 * x[6 + b]; s1[b] += a1 * x[6 + b]; s2[b] += a2 * x[9 + b]; s3[b] += a3 * x[9 + b]; }
+            }
+          }
+          if (cur >= 0) flush(cur);
         }
       }
       if (tid < kc) {
@@ -486,6 +526,25 @@ __global__ void __launch_bounds__(NT, 1) tile_kernel(View v, TileArgs a, Reduced
         const int kend = (3 * kc + 3) & ~3;
         const double* ybase = Yt + (size_t)gid * KK + tig;
         const double* gbase = Gt + (size_t)gid * KK + tig;
+        if constexpr (MAXS >= 24) {
+          // wide windows: the slots that end a block row were marked once per tile; the B fragment walks down Gt by a constant
+          // stride and restarts on the diagonal at a row end, so the loop is loads, DMMAs and one bit test per slot
+          const int rstride = 8 * KK;
+          for (int k0 = 0; k0 < kend; k0 += 4) {
+            const double* yk = ybase + k0;
+            const double* gk = gbase + k0;
+            int arow = bi0 * rstride, grow = bj0 * rstride;
+            double av = yk[arow];
+#pragma unroll
+            for (int sl = 0; sl < MAXS; sl++) {
+              if (sl < ns) {
+                dmma884(acc[sl][0], acc[sl][1], av, gk[grow]);
+                if ((rowend >> sl) & 1u) { arow += rstride; grow = arow; if (sl + 1 < ns) av = yk[arow]; }
+                else grow += rstride;
+              }
+            }
+          }
+        } else {
 #pragma unroll(MAXS <= 4 ? 4 : MAXS <= 8 ? 2 : 1)
         for (int k0 = 0; k0 < kend; k0 += 4) {
           int bi = bi0, bj = bj0;
@@ -498,6 +557,7 @@ __global__ void __launch_bounds__(NT, 1) tile_kernel(View v, TileArgs a, Reduced
               if (++bj == nb8) { bi++; bj = bi; if (sl + 1 < ns) av = ybase[(size_t)(8 * bi) * KK + k0]; }
             }
           }
+        }
         }
       }
       TPROF(5);

@@ -134,7 +134,7 @@ struct Solver {
   // (static round tables: staged blocks, per-track slots, gather groups and their contributors, kernels_tile.cuh)
   DBuf<int32_t> tile_w0, tile_wn, tile_round0, round_trk0, round_blk0, round_grp0, fallback;
   DBuf<TBlk> t_blk; DBuf<TTrk> t_trk; DBuf<TGrp> t_grp; DBuf<uint16_t> t_con;
-  int ntiles = 0, nrounds = 0, nfallback = 0, tile_nt = 512, tile_pr = 4, tile_K = 1, tile_icap = 64, tile_nx = 0, tile_L8max = 8, grid_tile = 1, tile_direct = 0;
+  int ntiles = 0, nrounds = 0, nfallback = 0, tile_nt = 512, tile_pr = 4, tile_K = 1, tile_icap = 64, tile_nx = 0, tile_L8max = 8, grid_tile = 1, tile_direct = 0, tile_nmono = 0;
   size_t smem_tile = 0;
   // pass B, staged variant (kernels_tile2.cuh): per-round blobs fetched by bulk copy, two CTAs per SM
   bool any_x = false, tile2 = false;
@@ -475,6 +475,12 @@ inline int solver_prepare(mvba_problem* h, bool with_F) {
       bool direct = nx >= 16;
       if (const char* ev = std::getenv("MVBA_TILE_DIRECT")) direct = nx > 0 && ev[0] == '1';   // developer switch
       s->tile_direct = direct;
+      s->tile_nmono = 0;
+      if (direct)
+        for (int t = 0; t < v.T; t++) {
+          const SensorDev& sd = v.sens[t];
+          if (sd.rpc_deg > 0 && (sd.c_dist >= 0 || sd.c_focal >= 0)) s->tile_nmono = std::max(s->tile_nmono, (sd.rpc_deg + 1) * (sd.rpc_deg + 2) / 2);
+        }
       int K = 32, icap = 0;  // phase b3 maps the staged tracks to the lanes of a warp
       for (; K >= 1; K--) {
         icap = (int)std::min<double>(511.0, std::max(32.0, std::ceil(1.15 * mean_items * K)));
