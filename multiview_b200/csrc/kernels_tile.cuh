@@ -56,6 +56,7 @@ struct TileArgs {
   int L8max;                  // padded local width the shared buffers are sized for
   int direct;                 // free non-pose columns go straight from phase b1 into Gt (no Xs staging, one round at a time)
   int nmono;                  // direct mode: monomials of the widest floating RPC model (0: none); phase b2 forms those columns
+  int cmode;                  // phase c loop of the wide instantiations: 0 the general loop, 1 branch-free in groups of eight slots
 };
 #define MVBA_XR 14            // per-block RPC record of direct mode: ux uy 1/den_x 1/den_y -ox/den_x -oy/den_y  sr Es[0..5]  Jf[0..1]
 
@@ -526,21 +527,28 @@ __global__ void __launch_bounds__(NT, 1) tile_kernel(View v, TileArgs a, Reduced
         const int kend = (3 * kc + 3) & ~3;
         const double* ybase = Yt + (size_t)gid * KK + tig;
         const double* gbase = Gt + (size_t)gid * KK + tig;
-        if constexpr (MAXS >= 24) {
-          // wide windows: the slots that end a block row were marked once per tile; the B fragment walks down Gt by a constant
-          // stride and restarts on the diagonal at a row end, so the loop is loads, DMMAs and one bit test per slot
+        if (MAXS >= 24 && a.cmode == 1) {
+          // wide windows, branch-free inside groups of eight slots: the slots that end a block row were marked once per tile; the
+          // B fragment walks down Gt by a constant stride and restarts on the diagonal at a row end; a slot beyond the warp's
+          // last block multiplies by zero (its loads read row 0)
           const int rstride = 8 * KK;
           for (int k0 = 0; k0 < kend; k0 += 4) {
             const double* yk = ybase + k0;
             const double* gk = gbase + k0;
             int arow = bi0 * rstride, grow = bj0 * rstride;
-            double av = yk[arow];
 #pragma unroll
-            for (int sl = 0; sl < MAXS; sl++) {
-              if (sl < ns) {
-                dmma884(acc[sl][0], acc[sl][1], av, gk[grow]);
-                if ((rowend >> sl) & 1u) { arow += rstride; grow = arow; if (sl + 1 < ns) av = yk[arow]; }
-                else grow += rstride;
+            for (int g8 = 0; g8 < MAXS; g8 += 8) {
+              if (g8 < ns) {
+#pragma unroll
+                for (int sl = g8; sl < g8 + 8; sl++) {
+                  const bool on = sl < ns;
+                  const double av = on ? yk[arow] : 0.0;
+                  const double bv = gk[on ? grow : 0];
+                  dmma884(acc[sl][0], acc[sl][1], av, bv);
+                  const bool end = (rowend >> sl) & 1u;
+                  arow += end ? rstride : 0;
+                  grow = end ? arow : grow + rstride;
+                }
               }
             }
           }
