@@ -56,7 +56,6 @@ struct TileArgs {
   int L8max;                  // padded local width the shared buffers are sized for
   int direct;                 // free non-pose columns go straight from phase b1 into Gt (no Xs staging, one round at a time)
   int nmono;                  // direct mode: monomials of the widest floating RPC model (0: none); phase b2 forms those columns
-  int cmode;                  // phase c loop of the wide instantiations: 0 the general loop, 1 branch-free in groups of eight slots
 };
 #define MVBA_XR 14            // per-block RPC record of direct mode: ux uy 1/den_x 1/den_y -ox/den_x -oy/den_y  sr Es[0..5]  Jf[0..1]
 
@@ -527,7 +526,7 @@ __global__ void __launch_bounds__(NT, 1) tile_kernel(View v, TileArgs a, Reduced
         const int kend = (3 * kc + 3) & ~3;
         const double* ybase = Yt + (size_t)gid * KK + tig;
         const double* gbase = Gt + (size_t)gid * KK + tig;
-        if (MAXS >= 24 && a.cmode == 1) {
+        if constexpr (MAXS >= 24) {
           // wide windows, branch-free inside groups of eight slots: the slots that end a block row were marked once per tile; the
           // B fragment walks down Gt by a constant stride and restarts on the diagonal at a row end; a slot beyond the warp's
           // last block multiplies by zero (its loads read row 0)

@@ -80,7 +80,6 @@ inline int run_build(mvba_problem* h, const mvba_solve_options& o, double radius
       ta.round_trk0 = s->round_trk0.p; ta.round_blk0 = s->round_blk0.p; ta.round_grp0 = s->round_grp0.p;
       ta.blk = s->t_blk.p; ta.ttrk = s->t_trk.p; ta.grp = s->t_grp.p; ta.con = s->t_con.p;
       ta.ntiles = s->ntiles; ta.K = s->tile_K; ta.icap = s->tile_icap; ta.nx = s->tile_nx; ta.L8max = s->tile_L8max; ta.direct = s->tile_direct; ta.nmono = s->tile_nmono; ta.coef = h->d_coef.p;
-      { static const int cmode = [] { const char* e = std::getenv("MVBA_TILE_CMODE"); return e ? std::atoi(e) : 0; }(); ta.cmode = cmode; }
       if (s->tile_nt == 256 && s->tile_pr == 24) tile_kernel<256, 24><<<s->grid_tile, 256, s->smem_tile, h->stream>>>(v, ta, s->R);
       else if (s->tile_nt == 256) tile_kernel<256, 32><<<s->grid_tile, 256, s->smem_tile, h->stream>>>(v, ta, s->R);
       else if (s->tile_pr == 4) tile_kernel<512, 4><<<s->grid_tile, 512, s->smem_tile, h->stream>>>(v, ta, s->R);
