@@ -266,3 +266,72 @@ def test_mesh_and_depth_flags(dataset, oracle_lib):
     o.close()
     assert got[0] == int((inl == 1).sum())
     assert abs(got[1] - s.initial_cost) <= 1e-4 * s.initial_cost and abs(got[2] - s.final_cost) <= 1e-4 * s.final_cost, (got, s.initial_cost, s.final_cost)
+
+
+def no_rig_problem(pr):
+    """The synthetic rig problem as --no_rig sees it: every image a camera of its own (sensor-major, time order inside a sensor,
+    lookupImagesNoBrackets), its pose the one the map holds (here: the rig-derived pose of the initial state)."""
+    import copy
+    order = np.lexsort((pr.cam_stamp, pr.cam_sensor))
+    inv = np.argsort(order)                                   # rig camera index -> no-rig camera index
+    Rm, tv = synth.world_to_cam_all(pr)
+    w2c = np.concatenate([tv, synth._mat_to_quat(Rm)], axis=1)[order]
+    q = copy.copy(pr)
+    q.no_rig = True
+    q.world_to_cam = np.ascontiguousarray(w2c.reshape(-1))
+    q.cam_sensor = np.ascontiguousarray(pr.cam_sensor[order]); q.cam_stamp = np.ascontiguousarray(pr.cam_stamp[order])
+    idx = np.concatenate([np.arange((q.cam_sensor == t).sum()) for t in range(len(pr.sensors))]).astype(np.int32)
+    q.cam_beg = idx.copy(); q.cam_end = idx.copy()
+    cid = inv[pr.cid].astype(np.int32)
+    o = np.lexsort((cid, pr.pid))
+    q.pid = np.ascontiguousarray(pr.pid[o]); q.cid = np.ascontiguousarray(cid[o])
+    q.pix = np.ascontiguousarray(pr.pix.reshape(-1, 2)[o].reshape(-1))
+    for nm in ("world_to_ref", "ref_to_cam", "offsets", "focal", "center", "distortion", "depth_to_image", "depth_scale", "xyz"):
+        setattr(q, nm, getattr(pr, nm).copy())
+    T = len(pr.sensors)
+    q.float_poses = np.ones(T, np.uint8); q.float_rig = np.zeros(T, np.uint8)
+    return q
+
+
+def test_no_rig_dry_run_lists_every_image_as_its_own_camera(dataset):
+    d, _ = dataset
+    pr = synth.make_problem(seed=31, sensors="rig3", num_ref=10, num_landmarks=120, obs_per_track=5)
+    q = no_rig_problem(pr)
+    out = run(d, "--dry_run", "--no_rig")
+    assert out.returncode == 0, out.stderr
+    got = json.loads(out.stdout)
+    cams = np.array(got["cams"])
+    assert np.array_equal(cams[:, 0], q.cam_sensor) and np.array_equal(cams[:, 1], q.cam_beg) and np.array_equal(cams[:, 2], q.cam_end)
+    assert np.array_equal(cams[:, 3], q.cam_stamp)
+    ff = np.array(got["first_features"])
+    assert np.array_equal(ff[:, 0], q.pid[:6]) and np.array_equal(ff[:, 1], q.cid[:6])
+
+
+@pytest.mark.gpu
+def test_no_rig_pass(dataset, oracle_lib):
+    """--no_rig: no bracketing, one free pose per image of the sensors named in --camera_poses_to_float (rig_calibrator.cc:1487-1492,
+    1669-1730), identity rig transforms in the written rig_config.txt (dense_map_utils.cc:836-839)."""
+    d, _ = dataset
+    pr = synth.make_problem(seed=31, sensors="rig3", num_ref=10, num_landmarks=120, obs_per_track=5)
+    names = [s.name for s in pr.sensors]
+    out = run(d, "--no_rig", "--calibrator_num_passes", "1", "--num_iterations", "2", "--camera_poses_to_float", " ".join(names),
+              "--min_triangulation_angle", "0.01")
+    assert out.returncode == 0, out.stderr + out.stdout[-2000:]
+    import re
+    m = re.search(r"pass 0: (\d+) inlier features, cost (\S+) -> (\S+) in", out.stdout)
+    got = (int(m.group(1)), float(m.group(2)), float(m.group(3)))
+    q = no_rig_problem(pr)
+    img = np.array([[s.width, s.height] for s in pr.sensors], np.float64)
+    o_all = _abi.Binding(oracle_lib, "oracle_", q)
+    inl = o_all.flag_exclusion(img, img)
+    xyz, inl = o_all.triangulate(inl, q.xyz)
+    o_all.close()
+    q.xyz[:] = xyz.ravel()
+    q2 = q.keep_observations(inl == 1)
+    o = _abi.Binding(oracle_lib, "oracle_", q2)
+    s, _ = o.solve(_abi.default_options(max_num_iterations=2), jac_mode=1, num_threads=1)
+    o.close()
+    assert got[0] == int((inl == 1).sum())
+    assert abs(got[1] - s.initial_cost) <= 1e-4 * s.initial_cost and abs(got[2] - s.final_cost) <= 1e-4 * s.final_cost, (got, s.initial_cost, s.final_cost)
+    rig_out = (d / "out" / "rig_config.txt").read_text()
+    assert rig_out.count("ref_to_sensor_transform: 1 0 0 0 1 0 0 0 1 0 0 0") == len(names)
