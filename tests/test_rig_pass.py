@@ -229,7 +229,8 @@ def depth_and_mesh_inputs(d, pr):
 
 
 @pytest.mark.gpu
-def test_mesh_and_depth_flags(dataset, oracle_lib):
+@pytest.mark.parametrize("affine", [False, True])
+def test_mesh_and_depth_flags(affine, dataset, oracle_lib):
     """--mesh (a .ply read by the driver, rays intersected on the device), depth clouds found beside the images, --depth_tri_weight,
     --depth_mesh_weight, --mesh_tri_weight, --depth_to_image_transforms_to_float and --float_scale: one pass against the oracle
     driven by hand through the same steps (rig_calibrator.cc:1582-1589, 1755-1840, 1857-1883)."""
@@ -239,10 +240,13 @@ def test_mesh_and_depth_flags(dataset, oracle_lib):
     # the fixture's rig_config.txt carries the identity as depth_to_image_transform for every sensor: the oracle's problem must too
     pr.depth_to_image[:] = np.tile([0, 0, 0, 0, 0, 0, 1.0], len(pr.sensors)); pr.depth_scale[:] = 1.0
     has, dxyz, verts, faces = depth_and_mesh_inputs(d, pr)
+    if affine:   # --affine_depth_to_image: twelve free numbers per floated depth transform, the scale block constant (rig_calibrator.cc:1445, 1787)
+        pr.affine_depth = True
+        pr.depth_to_image = np.tile([1.0, 0, 0, 0, 0, 1.0, 0, 0, 0, 0, 1.0, 0], len(pr.sensors))
     out = run(d, "--bracket_len", "1.0", "--calibrator_num_passes", "1", "--num_iterations", "4", "--use_initial_rig_transforms",
               "--camera_poses_to_float", names[0], "--rig_transforms_to_float", " ".join(names[1:]), "--mesh", str(d / "box.ply"),
               "--depth_tri_weight", "200", "--depth_mesh_weight", "20", "--mesh_tri_weight", "10", "--depth_to_image_transforms_to_float", names[1],
-              "--float_scale", "--min_triangulation_angle", "0.01", "--max_ray_dist", "50", cwd=str(d))
+              "--affine_depth_to_image" if affine else "--float_scale", "--min_triangulation_angle", "0.01", "--max_ray_dist", "50", cwd=str(d))
     assert out.returncode == 0, out.stderr + out.stdout[-2000:]
     for tag in ("depth_tri_x_m: ", "depth_mesh_x_m: ", "mesh_tri_x_m: "):
         assert tag in out.stdout, tag
@@ -251,7 +255,7 @@ def test_mesh_and_depth_flags(dataset, oracle_lib):
     got = (int(m.group(1)), float(m.group(2)), float(m.group(3)))
     T = len(pr.sensors)
     u8 = lambda v: np.array(v, np.uint8)
-    pr.float_poses = u8([1, 0, 0]); pr.float_rig = u8([0, 1, 1]); pr.float_d2i = u8([0, 1, 0]); pr.float_scale = True
+    pr.float_poses = u8([1, 0, 0]); pr.float_rig = u8([0, 1, 1]); pr.float_d2i = u8([0, 1, 0]); pr.float_scale = not affine
     pr.depth_tri_weight = 200.0; pr.depth_mesh_weight = 20.0
     img = np.array([[s.width, s.height] for s in pr.sensors], np.float64)
     o_all = _abi.Binding(oracle_lib, "oracle_", pr)
