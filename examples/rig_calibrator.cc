@@ -10,6 +10,8 @@
 // from the file name (interest_point.cc:1619-1627); a depth cloud is read from <image stem>.pc when that file exists (:1664-1669).
 // Flags whose work lies outside the bundle-adjustment path (--num_overlaps, --no_nvm_matches, --camera_poses, --registration,
 // --out_texture_dir, --save_matches, --export_to_voxblox, --save_transformed_depth_clouds) are parsed and validated, then refused.
+// Accepted without effect: --num_opt_threads (Ceres' thread count; it is passed on to updateRpcUndistortion like the reference does),
+// --num_match_threads, --initial_max_reprojection_error (the matcher's), --verbose, --hugin_file / --xyz_file without --registration.
 // One switch of its own: --dry_run stops before the first device call and prints the assembled pass (tests/test_rig_pass.py on a CPU box).
 // Exit codes: 1 command-line syntax (gflags), 2 a failed validation / input error (where the reference's LOG(FATAL) aborts), 3 a failed
 // device call (there is no CPU fallback).
